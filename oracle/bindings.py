@@ -1,0 +1,244 @@
+"""ctypes bindings of the CPU oracle (oracle/_build/libqrw_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: import this from tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs -- never from the product package.
+
+Every array is instance-major; inside an instance matrices are column-major (Eigen's layout),
+e.g. xref is [B, 12*(n+1)] with element (r, c) of instance b at [b, r + 12*c].
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "libqrw_oracle.so")
+_REF = os.path.join(_HERE, "_ref", "libst_to_cc.so")
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+def build(force=False):
+    """Compile the oracle (and oracle/_ref when /root/reference is present)."""
+    if force or not os.path.exists(_LIB) or any(
+        os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_LIB)
+        for f in os.listdir(_HERE)
+        if f.endswith((".cpp", ".hpp", ".h"))
+    ):
+        subprocess.check_call(["make", "-C", _HERE, "-s"], stdout=subprocess.DEVNULL)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB)
+        L.orc_mpc_create.restype = C.c_void_p
+        L.orc_mpc_create.argtypes = [C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]
+        L.orc_mpc_destroy.argtypes = [C.c_void_p]
+        L.orc_mpc_run.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.c_int]
+        L.orc_mpc_result.argtypes = [C.c_void_p, _dp]
+        L.orc_mpc_gait.argtypes = [C.c_void_p, _dp]
+        L.orc_mpc_sgait.argtypes = [C.c_void_p, _dp]
+        L.orc_mpc_info.argtypes = [C.c_void_p, _ip, _ip, _dp, _ip]
+        L.orc_mpc_nnz.argtypes = [C.c_void_p, C.c_int]
+        L.orc_mpc_ml.argtypes = [C.c_void_p, C.c_int, _dp, _ip, _ip]
+        L.orc_mpc_bounds.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
+        L.orc_mpc_solver_state.argtypes = [C.c_void_p, C.c_int] + [_dp] * 10
+        L.orc_mpc_set_trace.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_mpc_trace.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int]
+        L.orc_mpc_set_max_iter.argtypes = [C.c_void_p, C.c_int]
+        L.orc_wbc_create.restype = C.c_void_p
+        L.orc_wbc_create.argtypes = [C.c_int]
+        L.orc_wbc_destroy.argtypes = [C.c_void_p]
+        L.orc_wbc_run.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int]
+        L.orc_wbc_result.argtypes = [C.c_void_p, _dp, _dp, _dp]
+        L.orc_wbc_info.argtypes = [C.c_void_p, _ip, _ip, _dp]
+        L.orc_pinv6.argtypes = [_dp, _dp]
+        L.orc_invkin_run.argtypes = [C.c_int] + [_dp] * 12
+        L.orc_osqp_dense.argtypes = [C.c_int, C.c_int] + [_dp] * 5 + [C.c_double, C.c_int, _dp, _dp, _ip]
+        _lib = L
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def _i(a):
+    return a.ctypes.data_as(_ip)
+
+
+def _c(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class OracleMPC:
+    """Batch of independent restated `MPC` objects (reference src/MPC.cpp)."""
+
+    def __init__(self, batch=1, dt=0.02, n_steps=16, T_gait=0.32, N_gait=20):
+        self.B, self.n, self.N_gait = batch, n_steps, N_gait
+        self.h = lib().orc_mpc_create(batch, dt, n_steps, T_gait, N_gait)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_mpc_destroy(self.h)
+            self.h = None
+
+    def run(self, num_iter, xref, fsteps, nthreads=1):
+        xref, fsteps = _c(xref), _c(fsteps)
+        assert xref.size == self.B * 12 * (self.n + 1) and fsteps.size == self.B * 12 * self.N_gait
+        lib().orc_mpc_run(self.h, int(num_iter), _d(xref), _d(fsteps), int(nthreads))
+        return 0
+
+    def get_latest_result(self):
+        out = np.empty((self.B, 24 * self.n))
+        lib().orc_mpc_result(self.h, _d(out))
+        return out
+
+    def get_gait(self):
+        out = np.empty((self.B, 4 * self.N_gait))
+        lib().orc_mpc_gait(self.h, _d(out))
+        return out
+
+    def get_Sgait(self):
+        out = np.empty((self.B, 12 * self.n))
+        lib().orc_mpc_sgait(self.h, _d(out))
+        return out
+
+    def info(self):
+        it = np.empty(self.B, np.int32)
+        stt = np.empty(self.B, np.int32)
+        rho = np.empty(self.B)
+        nf = np.empty(self.B, np.int32)
+        lib().orc_mpc_info(self.h, _i(it), _i(stt), _d(rho), _i(nf))
+        return dict(iters=it, status=stt, rho=rho, n_factor=nf)
+
+    def ml(self, b=0):
+        nnz = lib().orc_mpc_nnz(self.h, b)
+        x = np.empty(nnz)
+        ri = np.empty(nnz, np.int32)
+        cp = np.empty(24 * self.n + 1, np.int32)
+        lib().orc_mpc_ml(self.h, b, _d(x), _i(ri), _i(cp))
+        return x, ri, cp
+
+    def bounds(self, b=0):
+        l = np.empty(44 * self.n)
+        u = np.empty(44 * self.n)
+        lib().orc_mpc_bounds(self.h, b, _d(l), _d(u))
+        return l, u
+
+    def solver_state(self, b=0):
+        n, m = 24 * self.n, 44 * self.n
+        nnz = lib().orc_mpc_nnz(self.h, b)
+        D, E, c = np.empty(n), np.empty(m), np.empty(1)
+        x, z, y = np.empty(n), np.empty(m), np.empty(m)
+        As, Ps, ls, us = np.empty(nnz), np.empty(n), np.empty(m), np.empty(m)
+        lib().orc_mpc_solver_state(self.h, b, _d(D), _d(E), _d(c), _d(x), _d(z), _d(y), _d(As), _d(Ps), _d(ls), _d(us))
+        return dict(D=D, E=E, c=c[0], x=x, z=z, y=y, A=As, P=Ps, l=ls, u=us)
+
+    def set_trace(self, b=0, on=True):
+        lib().orc_mpc_set_trace(self.h, b, int(on))
+
+    def trace(self, b=0):
+        nrow = lib().orc_mpc_trace(self.h, b, None, 0)
+        out = np.empty((nrow, 4))
+        lib().orc_mpc_trace(self.h, b, _d(out), nrow)
+        return out
+
+    def set_max_iter(self, k):
+        lib().orc_mpc_set_max_iter(self.h, int(k))
+
+
+class OracleWBC:
+    """Batch of independent restated `QPWBC` objects (reference src/QPWBC.cpp)."""
+
+    def __init__(self, batch=1):
+        self.B = batch
+        self.h = lib().orc_wbc_create(batch)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_wbc_destroy(self.h)
+            self.h = None
+
+    def run(self, M, Jc, f_cmd, RNEA, nthreads=1):
+        M, Jc, f_cmd, RNEA = _c(M), _c(Jc), _c(f_cmd), _c(RNEA)
+        assert M.size == self.B * 324 and Jc.size == self.B * 216
+        lib().orc_wbc_run(self.h, _d(M), _d(Jc), _d(f_cmd), _d(RNEA), int(nthreads))
+        return 0
+
+    def results(self):
+        f, d, H = np.empty((self.B, 12)), np.empty((self.B, 6)), np.empty((self.B, 144))
+        lib().orc_wbc_result(self.h, _d(f), _d(d), _d(H))
+        return f, d, H
+
+    def info(self):
+        it = np.empty(self.B, np.int32)
+        stt = np.empty(self.B, np.int32)
+        rho = np.empty(self.B)
+        lib().orc_wbc_info(self.h, _i(it), _i(stt), _d(rho))
+        return dict(iters=it, status=stt, rho=rho)
+
+
+def invkin(contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf):
+    """Batched restated InvKin::refreshAndCompute (reference src/InvKin.cpp:23-73)."""
+    B = _c(contacts).size // 4
+    args = [_c(a) for a in (contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf)]
+    ddq, dq, qs = np.empty((B, 12)), np.empty((B, 12)), np.empty((B, 12))
+    lib().orc_invkin_run(B, *[_d(a) for a in args], _d(ddq), _d(dq), _d(qs))
+    return ddq, dq, qs
+
+
+def pinv6(a):
+    a = np.asfortranarray(a, dtype=np.float64)
+    out = np.empty((6, 6), order="F")
+    lib().orc_pinv6(_d(a), _d(out))
+    return out
+
+
+def osqp_dense(P, A, q, l, u, eps=1e-8, max_iter=20000):
+    """Restated OSQP on a dense problem; returns (x, y, iters, status)."""
+    P = np.asfortranarray(P, dtype=np.float64)
+    A = np.asfortranarray(A, dtype=np.float64)
+    m, n = A.shape
+    q, l, u = _c(q), _c(l), _c(u)
+    x, y = np.empty(n), np.empty(m)
+    it = np.zeros(1, np.int32)
+    st = lib().orc_osqp_dense(n, m, _d(P), _d(A), _d(q), _d(l), _d(u), float(eps), int(max_iter), _d(x), _d(y), _i(it))
+    return x, y, int(it[0]), st
+
+
+# ---------------------------------------------------------------------------------------------
+# Reference-built converter (oracle/_ref): the reference's own src/st_to_cc.cpp compiled in place.
+# ---------------------------------------------------------------------------------------------
+def ref_st_to_cc_available():
+    return os.path.exists(_REF)
+
+
+def ref_st_to_cc(rows, cols, vals, n_cols):
+    """Run the REFERENCE st_to_cc_size/index/values on a triplet list; returns (icc, ccc, acc)."""
+    L = C.CDLL(_REF)
+    # C++ symbols (the reference builds this file as C++): look them up by mangled name
+    size = getattr(L, "_Z13st_to_cc_sizeiPiS_")
+    index = getattr(L, "_Z14st_to_cc_indexiPiS_iiS_S_")
+    values = getattr(L, "_Z15st_to_cc_valuesiPiS_PdiiS_S_")
+    rows = np.ascontiguousarray(rows, np.int32)
+    cols = np.ascontiguousarray(cols, np.int32)
+    vals = _c(vals)
+    nst = rows.size
+    size.restype = C.c_int
+    ncc = size(nst, _i(rows), _i(cols))
+    icc = np.zeros(ncc, np.int32)
+    ccc = np.zeros(n_cols + 1, np.int32)
+    index(nst, _i(rows), _i(cols), ncc, n_cols, _i(icc), _i(ccc))
+    values.restype = _dp
+    p = values(nst, _i(rows), _i(cols), _d(vals), ncc, n_cols, _i(icc), _i(ccc))
+    acc = np.array([p[k] for k in range(ncc)])
+    return icc, ccc, acc

@@ -1,0 +1,51 @@
+// qrw_spmd.cuh -- warp-SPMD portability layer.
+//
+// The solver cores (mpc_core.cuh, wbc_core.cuh) are written as a sequence of "phases": a phase
+// body runs once per lane of ONE warp, phases are separated by warp barriers, and all
+// cross-lane traffic goes through the warp's shared-memory slab.  Under nvcc a phase body is
+// executed by the 32 hardware lanes; under a plain C++ compiler (tests/emu, -DQRW_EMULATE) the
+// same source runs the 32 lanes one after the other, which lets the kernel logic be checked
+// against the CPU oracle on a machine without a GPU.  The emulation build is test
+// infrastructure only -- the shipped library contains the CUDA build and nothing else.
+//
+// Rules that keep both builds equivalent:
+//   * inside one phase a lane never reads a shared location another lane writes in that phase;
+//   * code between phases ("uniform code") only reads shared memory (or writes values every
+//     lane agrees on) and computes lane-invariant scalars.
+#pragma once
+
+#if defined(__CUDACC__) && !defined(QRW_EMULATE)
+#define QRW_HD __device__ __forceinline__
+#define QRW_HDN __device__ __noinline__
+#define QRW_LANES(l) for (int l = (int)(threadIdx.x & 31), _once = 1; _once; _once = 0)
+#define QRW_SYNC() __syncwarp()
+#define QRW_ON_GPU 1
+#else
+#define QRW_HD inline
+#define QRW_HDN inline
+#define QRW_LANES(l) for (int l = 0; l < 32; ++l)
+#define QRW_SYNC() ((void)0)
+#define QRW_ON_GPU 0
+#include <cmath>
+#endif
+
+namespace qrw {
+
+QRW_HD double dmax(double a, double b) { return a > b ? a : b; }
+QRW_HD double dmin(double a, double b) { return a < b ? a : b; }
+
+// max over the 32 per-lane partials red[0..31] (uniform code; callers sync before and after)
+QRW_HD double red_max32(const double* red) {
+  double m = red[0];
+#pragma unroll
+  for (int i = 1; i < 32; ++i) m = dmax(m, red[i]);
+  return m;
+}
+QRW_HD double red_sum32(const double* red) {
+  double m = red[0];
+#pragma unroll
+  for (int i = 1; i < 32; ++i) m += red[i];
+  return m;
+}
+
+}  // namespace qrw

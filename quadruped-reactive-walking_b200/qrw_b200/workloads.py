@@ -1,0 +1,164 @@
+"""Synthetic inputs for the BASELINE.json configs.
+
+Host-side numpy only.  The generators restate, in vectorised form, what the reference's input
+producers hand to `MPC.run`:
+
+* reference states `xref` (12 x (n+1)) -- StatePlanner::computeReferenceStates,
+  /root/reference/src/StatePlanner.cpp:21-60
+* contact schedules -- Gait::create_trot / create_walk / create_pacing / create_bounding /
+  create_static, /root/reference/src/Gait.cpp:38-108, rolled one row per MPC tick (Gait.cpp:221-260)
+* footstep matrix `fsteps` (N_gait x 12): one (x, y, 0) foothold per foot in contact, exactly 0.0
+  for swing feet (that is how MPC::construct_gait detects them, src/MPC.cpp:686-701); footholds
+  are the Solo12 shoulders (scripts/Controller.py:131-133) plus uniform noise.
+
+Layouts are the batched C-ABI's: instance-major, column-major inside an instance
+(`xref[b, r + 12*c]`, `fsteps[b, k + N_gait*j]`).
+"""
+import numpy as np
+
+DT_MPC = 0.02
+N_STEPS = 16
+T_GAIT = 0.32
+N_GAIT = 20
+H_REF = 0.2027682065963745  # (double)0.2027682f, src/MPC.cpp:27-28
+Z_INIT = 0.24474949993103629  # scripts/test_mpc.py:39
+SHOULDERS = np.array([[0.1946, 0.1946, -0.1946, -0.1946], [0.14695, -0.14695, 0.14695, -0.14695]])
+
+GAITS = ("trot", "walk", "bounding", "pacing", "static")
+
+
+def gait_cycle(name, n=N_STEPS):
+    """One period (n rows x 4) of the named gait, rows of 0/1 (Gait.cpp:38-108)."""
+    g = np.zeros((n, 4))
+    h, q = n // 2, n // 4
+    if name == "trot":
+        g[:h] = [1, 0, 0, 1]
+        g[h:] = [0, 1, 1, 0]
+    elif name == "pacing":
+        g[:h] = [1, 0, 1, 0]
+        g[h:] = [0, 1, 0, 1]
+    elif name == "bounding":
+        g[:h] = [1, 1, 0, 0]
+        g[h:] = [0, 0, 1, 1]
+    elif name == "walk":
+        g[:] = 1
+        for i in range(4):
+            g[i * q:(i + 1) * q, i] = 0
+    elif name == "static":
+        g[:] = 1
+    else:
+        raise ValueError(name)
+    return g
+
+
+def reference_states(x0, vref, n=N_STEPS, dt=DT_MPC, h_ref=H_REF, z_average=0.0):
+    """Vectorised StatePlanner::computeReferenceStates.  x0: [B,12] current state in the
+    horizontal frame (x = y = yaw = 0 are imposed as the reference does), vref: [B,6].
+    Returns xref [B, 12, n+1]."""
+    B = x0.shape[0]
+    xr = np.zeros((B, 12, n + 1))
+    xr[:, 2, 0] = x0[:, 2]
+    xr[:, 3:5, 0] = x0[:, 3:5]
+    xr[:, 6:12, 0] = x0[:, 6:12]
+    t = np.linspace(dt, n * dt, n)[None, :]  # dt_vector_
+    vx, vy, wz = vref[:, 0:1], vref[:, 1:2], vref[:, 5:6]
+    nz = wz != 0
+    wz_safe = np.where(nz, wz, 1.0)
+    xr[:, 0, 1:] = np.where(nz, (vx * np.sin(wz * t) + vy * (np.cos(wz * t) - 1.0)) / wz_safe, vx * t)
+    xr[:, 1, 1:] = np.where(nz, (vy * np.sin(wz * t) - vx * (np.cos(wz * t) - 1.0)) / wz_safe, vy * t)
+    xr[:, 2, 1:] = h_ref + z_average
+    yaw = wz * t
+    xr[:, 5, 1:] = yaw
+    xr[:, 6, 1:] = vx * np.cos(yaw) - vy * np.sin(yaw)
+    xr[:, 7, 1:] = vx * np.sin(yaw) + vy * np.cos(yaw)
+    xr[:, 11, 1:] = wz
+    return xr
+
+
+class MpcWorkload:
+    """A batch of B robots with a gait timeline long enough for `ticks` rolled MPC calls.
+
+    inputs(t, x0) gives the (xref, fsteps) of MPC tick t with the current state x0 ([B,12], or None
+    for the initial random state) in the C-ABI layout.
+    """
+
+    def __init__(self, B, seed, gaits=("trot",), ticks=9, n=N_STEPS, N_gait=N_GAIT):
+        rng = np.random.default_rng(seed)
+        self.B, self.n, self.N_gait, self.ticks = B, n, N_gait, ticks
+        # random initial state (ranges of scripts/test_mpc.py:93) and velocity reference
+        # (envelope of scripts/Joystick.py:207-278)
+        x0 = np.zeros((B, 12))
+        x0[:, 2] = rng.uniform(0.18, 0.26, B)
+        x0[:, 3:5] = rng.uniform(-0.1, 0.1, (B, 2))
+        x0[:, 6:9] = rng.uniform(-0.3, 0.3, (B, 3))
+        x0[:, 9:12] = rng.uniform(-0.4, 0.4, (B, 3))
+        self.x0 = x0
+        vref = np.zeros((B, 6))
+        vref[:, 0] = rng.uniform(-0.5, 1.5, B)
+        vref[:, 1] = rng.uniform(-0.5, 0.5, B)
+        vref[:, 5] = rng.uniform(-0.7, 0.7, B)
+        self.vref = vref
+        # gait timeline: rows t .. t+n-1 are the horizon of tick t
+        L = ticks + n
+        self.kind = rng.integers(0, len(gaits), B)
+        phase = rng.integers(0, n, B)
+        cycles = np.stack([gait_cycle(g, n) for g in gaits])  # [G, n, 4]
+        rows = (phase[:, None] + np.arange(L)[None, :]) % n  # [B, L]
+        self.timeline = cycles[self.kind[:, None], rows]  # [B, L, 4]
+        # one foothold per contiguous stance segment of each foot
+        noise = rng.uniform(-0.05, 0.05, (B, L, 4, 2))
+        start = np.ones((B, L, 4), bool)
+        start[:, 1:] = self.timeline[:, 1:] != self.timeline[:, :-1]
+        seg_id = np.cumsum(start, axis=1) - 1  # [B, L, 4]
+        seg_noise = np.take_along_axis(noise, np.broadcast_to(seg_id[..., None], noise.shape), axis=1)
+        # index trick above picks noise[b, seg_id, foot]: constant inside a segment
+        pos = np.zeros((B, L, 4, 3))
+        pos[..., 0] = SHOULDERS[0][None, None, :] + seg_noise[..., 0]
+        pos[..., 1] = SHOULDERS[1][None, None, :] + seg_noise[..., 1]
+        self.footholds = pos * self.timeline[..., None]  # swing feet exactly 0.0
+
+    def gait(self, t):
+        """gait matrix the reference planner would hold at tick t: [B, N_gait, 4]."""
+        g = np.zeros((self.B, self.N_gait, 4))
+        g[:, : self.n] = self.timeline[:, t:t + self.n]
+        return g
+
+    def inputs(self, t, x0=None):
+        x0 = self.x0 if x0 is None else x0
+        xr = reference_states(x0, self.vref, self.n)
+        # closed loop as scripts/test_mpc.py:78 -- the whole predicted state becomes column 0
+        xr[:, :, 0] = x0
+        fs = np.zeros((self.B, self.N_gait, 12))
+        fs[:, : self.n] = self.footholds[:, t:t + self.n].reshape(self.B, self.n, 12)
+        xref = np.ascontiguousarray(xr.transpose(0, 2, 1)).reshape(self.B, 12 * (self.n + 1))
+        fsteps = np.ascontiguousarray(fs.transpose(0, 2, 1)).reshape(self.B, 12 * self.N_gait)
+        return xref, fsteps
+
+
+def config1_single_trot():
+    """BASELINE config 1: the single trot solve of scripts/test_mpc.py:136-146 (current signature:
+    12-column fsteps, no duration column).  Returns (xref [1,204], fsteps [1,240])."""
+    xr = np.zeros((12, N_STEPS + 1))
+    xr[2, :] = Z_INIT
+    fs = np.zeros((N_GAIT, 12))
+    pair_1 = np.array([0.195, 0.147, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, -0.195, -0.147, 0.0])
+    pair_2 = np.array([0.0, 0.0, 0.0, 0.195, -0.147, 0.0, -0.195, 0.147, 0.0, 0.0, 0.0, 0.0])
+    fs[0:8] = pair_1
+    fs[8:16] = pair_2
+    return xr.T.reshape(1, -1).copy(), fs.T.reshape(1, -1).copy()
+
+
+def four_stance(x0=None):
+    """scripts/test_mpc.py:54-58 -- four feet on the ground for the whole horizon."""
+    xr = np.zeros((12, N_STEPS + 1))
+    xr[2, :] = Z_INIT
+    if x0 is not None:
+        xr[:, 0] = x0
+    fs = np.zeros((N_GAIT, 12))
+    fs[0:16] = np.array([0.195, 0.147, 0.0, 0.195, -0.147, 0.0, -0.195, 0.147, 0.0, -0.195, -0.147, 0.0])
+    return xr.T.reshape(1, -1).copy(), fs.T.reshape(1, -1).copy()
+
+
+def next_state(result, n=N_STEPS):
+    """Predicted next state x_f_applied[:12, 0] of every instance: result is [B, 24*n]."""
+    return result[:, :12].copy()

@@ -1,0 +1,40 @@
+// tests/emu/emu_kernels.cpp -- TEST INFRASTRUCTURE.  Compiles the product's kernel cores
+// (csrc/*_core.cuh) with a plain C++ compiler in warp-emulation mode (-DQRW_EMULATE, see
+// csrc/qrw_spmd.cuh) so their logic can be checked against the CPU oracle on a machine that has
+// no GPU.  It is never loaded by the product and is not a CPU fallback.
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../quadruped-reactive-walking_b200/csrc/mpc_core.cuh"
+
+using namespace qrw;
+
+extern "C" {
+
+int emu_mpc_state_doubles() { return MPC_STATE_DOUBLES; }
+int emu_mpc_state_ints() { return MPC_STATE_INTS; }
+
+// Same contract as the CUDA kernel: instance-major inputs, persistent state, outputs.
+void emu_mpc_run(int B, double dt, int N_gait, int first, int max_iter, const double* xref,
+                 const double* fsteps, double* st_d, int* st_i, double* out, int* info, double* rho,
+                 double* dbg, int nthreads) {
+  MpcConst C = make_mpc_const(dt, N_gait);
+  if (max_iter > 0) C.max_iter = max_iter;
+  auto work = [&](int t) {
+    std::vector<double> slab(MPC_SLAB_DOUBLES, 0.0);
+    for (int b = t; b < B; b += nthreads)
+      mpc_solve_instance(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
+                         st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                         out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+  };
+  if (nthreads <= 1) {
+    nthreads = 1;
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+    for (auto& t : th) t.join();
+  }
+}
+}
