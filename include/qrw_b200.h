@@ -1,0 +1,112 @@
+/* qrw_b200.h -- C ABI of the B200-native batched controller core (libqrw_b200.so).
+ *
+ * Drop-in boundary for the per-tick hot path of paLeziart/quadruped-reactive-walking.  Each
+ * entry point replaces a method the reference exposes through Boost.Python
+ * (/root/reference/python/gepadd.cpp) on the C++ classes MPC, QPWBC and InvKin; the reference
+ * handles ONE robot per object on the CPU, these handle a batch of B independent robots per
+ * object on one GPU.  INTEGRATION.md shows the binding a maintainer would add on the
+ * reference side.
+ *
+ * Conventions
+ *  - plain C: opaque handles, pointers and sizes, int return codes (0 = ok, non-zero = error,
+ *    text from qrw_last_error()).  No C++ or torch types, no exceptions across the boundary.
+ *  - every array is instance-major; inside one instance matrices are COLUMN-MAJOR doubles,
+ *    i.e. exactly what Eigen::MatrixXd::data() holds in the reference:
+ *        xref   [B][12*(n_steps+1)]   element (r,c) at r + 12*c          (MPC.cpp:626 xref_in)
+ *        fsteps [B][N_gait*12]        element (k,j) at k + N_gait*j      (MPC.cpp:626 fsteps_in)
+ *        result [B][24*n_steps]       element (r,i) at r + 24*i          (MPC.cpp:604)
+ *  - "_device" entry points take device pointers and are asynchronous on the given CUDA stream
+ *    (pass a cudaStream_t cast to void*, NULL = default stream); "_host" entry points take host
+ *    pointers, do the H2D / D2H copies themselves and return when the data is there.
+ *  - there is no CPU fallback: every call fails with an error if no CUDA device is usable.
+ */
+#ifndef QRW_B200_H
+#define QRW_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct qrw_mpc qrw_mpc_t;
+typedef struct qrw_wbc qrw_wbc_t;
+
+const char* qrw_last_error(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+long long qrw_launch_count(void);
+int qrw_device_sm_count(int device, int* sm_count);
+/* measured FP64 FMA throughput of `device` in TFLOP/s (DFMA microbenchmark; the denominator of the
+ * FP64 roofline fraction bench.py reports next to the HBM one) */
+int qrw_fp64_peak(int device, double* tflops);
+
+/* ---------------------------------------------------------------------------------------
+ * MPC -- replaces class MPC (include/qrw/MPC.hpp:16-129, src/MPC.cpp)
+ * ------------------------------------------------------------------------------------- */
+/* MPC::MPC(dt, n_steps, T_gait, N_gait), src/MPC.cpp:3-32, for `batch` robots on `device`.
+ * Only the reference configuration n_steps == 16 is compiled in (src/config_solo12.yaml:11-13);
+ * n_steps < N_gait <= 32. */
+int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_gait, int N_gait, int device);
+int qrw_mpc_destroy(qrw_mpc_t* h);
+/* MPC::run(num_iter, xref_in, fsteps_in), src/MPC.cpp:626-649.  num_iter == 0 takes the
+ * create_matrices/osqp_setup path (cold start), anything else the update path (warm start from
+ * the state left by the previous call).  One value for the whole batch. */
+int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const double* d_fsteps, void* stream);
+int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const double* fsteps);
+/* MPC::get_latest_result(), src/MPC.cpp:604: [B][24*n_steps] */
+int qrw_mpc_result_host(qrw_mpc_t* h, double* out);
+int qrw_mpc_result_device(qrw_mpc_t* h, const double** d_out);
+/* MPC::get_gait() / get_Sgait(), src/MPC.cpp:770-780: [B][N_gait*4] and [B][12*n_steps] doubles */
+int qrw_mpc_gait_host(qrw_mpc_t* h, double* out);
+int qrw_mpc_sgait_host(qrw_mpc_t* h, double* out);
+/* what OSQP keeps in work->info and the reference throws away (src/MPC.cpp:558-563):
+ * per-instance ADMM iterations, OSQP status value, rho after the solve, KKT factorisations.
+ * Any pointer may be NULL. */
+int qrw_mpc_info_host(qrw_mpc_t* h, int* iters, int* status, double* rho, int* n_factor);
+/* test hooks: iteration cap (default 4000, OSQP max_iter) and a dump of the Ruiz scaling
+ * (D[384] | E[704] | c | unscaled dynamics bounds[192]) of every instance after the next run */
+int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter);
+int qrw_mpc_debug_host(qrw_mpc_t* h, double* out /* [B][1281] */);
+/* The solver state carried from call to call (scaled ADMM iterates, rho, stale B_k values, gait,
+ * S_gait -- the reference keeps it inside OSQP's workspace and the MPC object).  Snapshot and
+ * restore, e.g. to replay a benchmark from the same history or to checkpoint a fleet. */
+int qrw_mpc_state_bytes(qrw_mpc_t* h, size_t* bytes);
+int qrw_mpc_state_save(qrw_mpc_t* h, void* d_buf, void* stream);
+int qrw_mpc_state_load(qrw_mpc_t* h, const void* d_buf, void* stream);
+/* pinned host staging owned by the handle (inputs / result), for callers that want their
+ * host<->device copies to be truly asynchronous */
+int qrw_mpc_pinned(qrw_mpc_t* h, double** xref, double** fsteps, double** result);
+
+/* ---------------------------------------------------------------------------------------
+ * QPWBC -- replaces class QPWBC (include/qrw/QPWBC.hpp:16-98, src/QPWBC.cpp)
+ * ------------------------------------------------------------------------------------- */
+int qrw_wbc_create(qrw_wbc_t** out, int batch, int device);
+int qrw_wbc_destroy(qrw_wbc_t* h);
+/* QPWBC::run(M, Jc, f_cmd, RNEA, k_contact), src/QPWBC.cpp:310-343 (k_contact is accepted and
+ * ignored by the reference, :345-362; it is not part of this ABI).
+ * M [B][18*18], Jc [B][12*18], f_cmd [B][12], RNEA [B][6]. */
+int qrw_wbc_run_device(qrw_wbc_t* h, const double* d_M, const double* d_Jc, const double* d_f_cmd,
+                       const double* d_RNEA, void* stream);
+int qrw_wbc_run_host(qrw_wbc_t* h, const double* M, const double* Jc, const double* f_cmd, const double* RNEA);
+/* get_f_res [B][12], get_ddq_res [B][6], get_H [B][144] (src/QPWBC.cpp:302-308); NULL skips */
+int qrw_wbc_result_host(qrw_wbc_t* h, double* f_res, double* ddq_res, double* H);
+int qrw_wbc_result_device(qrw_wbc_t* h, const double** d_f_res, const double** d_ddq_res);
+int qrw_wbc_info_host(qrw_wbc_t* h, int* iters, int* status, double* rho);
+
+/* ---------------------------------------------------------------------------------------
+ * InvKin -- replaces InvKin::refreshAndCompute (src/InvKin.cpp:23-73); stateless.
+ * contacts [B][4]; goals, vgoals, agoals [B][3*4]; posf, vf, wf, af [B][4*3]; Jf [B][12*12];
+ * outputs ddq (return value), dq_cmd (get_dq_cmd), q_step (get_q_step): [B][12] each.
+ * ------------------------------------------------------------------------------------- */
+int qrw_invkin_run_device(int batch, const double* contacts, const double* goals, const double* vgoals,
+                          const double* agoals, const double* posf, const double* vf, const double* wf,
+                          const double* af, const double* Jf, double* ddq, double* dq_cmd, double* q_step,
+                          void* stream);
+int qrw_invkin_run_host(int batch, const double* contacts, const double* goals, const double* vgoals,
+                        const double* agoals, const double* posf, const double* vf, const double* wf,
+                        const double* af, const double* Jf, double* ddq, double* dq_cmd, double* q_step);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QRW_B200_H */

@@ -47,6 +47,7 @@ struct Mpc {
   std::vector<double> x_f_applied;  // 24 x n col-major
   Osqp osqp;
   bool gait_overrun = false;  // reference would read out of bounds (no all-zero row in fsteps)
+  int max_iter_override = 0;  // test hook (0 = OSQP default 4000)
 
   Mpc(double dt_in, int n_steps_in, double T_gait_in, int N_gait_in) {  // MPC.cpp:3-32
     dt = dt_in;
@@ -328,6 +329,7 @@ struct Mpc {
     s.adaptive_rho = 1;
     s.adaptive_rho_interval = 200;
     s.adaptive_rho_tolerance = 5.0;
+    if (max_iter_override > 0) s.max_iter = max_iter_override;
     return s;
   }
 
@@ -729,7 +731,10 @@ int orc_mpc_trace(void* hv, int b, double* out, int cap) {  // rows of (iter, pr
   return nrow;
 }
 void orc_mpc_set_max_iter(void* hv, int max_iter) {  // test hook only
-  for (auto* p : ((MpcBatch*)hv)->inst) p->osqp.st.max_iter = max_iter;
+  for (auto* p : ((MpcBatch*)hv)->inst) {
+    p->max_iter_override = max_iter;
+    p->osqp.st.max_iter = max_iter;
+  }
 }
 
 // ---- QPWBC ----

@@ -84,10 +84,6 @@ struct MpcSlab {
 };
 
 QRW_HD int sym_idx(int a, int b) { return a >= b ? (a * (a + 1)) / 2 + b : (b * (b + 1)) / 2 + a; }
-QRW_HD double limit_scaling(double v) {
-  v = v < 1e-4 ? 1.0 : v;
-  return v > 1e4 ? 1e4 : v;
-}
 // global index of stage-local variable a of stage k: a<12 -> force f_k[a], else X_{k+1}[a-12]
 QRW_HD int gvar(int k, int a) { return a < 12 ? 192 + 12 * k + a : 12 * k + (a - 12); }
 

@@ -1,0 +1,609 @@
+// qrw_b200.cu -- kernels + C ABI (include/qrw_b200.h) of the batched controller core.
+//
+// Build (see __graft_entry__.build()):
+//   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared \
+//        -Xcompiler -fPIC -o libqrw_b200.so qrw_b200.cu
+// Plain CUDA runtime only -- no torch, no cuBLAS.  There is no CPU fallback in this library.
+//
+// Execution model: a persistent grid of one-warp CTAs (three per SM for the MPC: each owns a
+// 75 KB shared-memory slab holding one instance's whole solver state) pulls instance indices
+// from a global work counter, so the large spread of ADMM iteration counts across a batch
+// (25 ... 4000) does not leave SMs idle behind a slow instance.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/qrw_b200.h"
+#include "mpc_core.cuh"
+#include "wbc_core.cuh"
+
+using namespace qrw;
+
+namespace {
+
+thread_local std::string g_err;
+long long g_launches = 0;
+
+int fail(const std::string& what) {
+  g_err = what;
+  return 1;
+}
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(std::string(#call) + ": " + cudaGetErrorString(e_));                    \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) mpc_solve_kernel(const MpcConst C, const int B, const int first,
+                                                       const double* __restrict__ xref,
+                                                       const double* __restrict__ fsteps, double* st_d,
+                                                       int* st_i, double* out, int* info, double* rho,
+                                                       double* dbg, int* counter) {
+  extern __shared__ __align__(16) double slab[];
+  const int lane = threadIdx.x;
+  for (;;) {
+    int b = 0;
+    if (lane == 0) b = atomicAdd(counter, 1);
+    b = __shfl_sync(0xffffffffu, b, 0);
+    if (b >= B) break;
+    mpc_solve_instance(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
+                       st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                       out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+    __syncwarp();
+  }
+}
+
+// gait / S_gait as the doubles the reference getters return (MPC.cpp:770-780)
+__global__ void mpc_unpack_gait_kernel(const int* st_i, int B, int N_gait, double* gait, double* sgait) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = 4 * N_gait + 12 * NS;
+  if (t >= B * per) return;
+  const int b = t / per, e = t - b * per;
+  const int* s = st_i + (size_t)b * MPC_STATE_INTS;
+  if (e < 4 * N_gait) {
+    const int i = e / N_gait, k = e - N_gait * i;  // column-major N_gait x 4
+    gait[(size_t)b * 4 * N_gait + e] = (double)((s[k] >> i) & 1);
+  } else {
+    const int q = e - 4 * N_gait, k = q / 12, a = q - 12 * k;
+    sgait[(size_t)b * 12 * NS + q] = (double)((s[32 + k] >> (a / 3)) & 1);
+  }
+}
+
+constexpr int WBC_WARPS = 4;
+__global__ void __launch_bounds__(32 * WBC_WARPS) wbc_solve_kernel(const WbcConst C, const int B, const int first,
+                                                                  const double* __restrict__ M,
+                                                                  const double* __restrict__ Jc,
+                                                                  const double* __restrict__ f_cmd,
+                                                                  const double* __restrict__ RNEA, double* st,
+                                                                  double* f_res, double* ddq_res, double* H,
+                                                                  int* info, int* counter) {
+  extern __shared__ __align__(16) double slab[];
+  double* sl = slab + (threadIdx.x >> 5) * WBC_SLAB_DOUBLES;
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    int b = 0;
+    if (lane == 0) b = atomicAdd(counter, 1);
+    b = __shfl_sync(0xffffffffu, b, 0);
+    if (b >= B) break;
+    wbc_solve_instance(C, sl, M + (size_t)b * 324, Jc + (size_t)b * 216, f_cmd + (size_t)b * 12,
+                       RNEA + (size_t)b * 6, st + (size_t)b * WBC_STATE_DOUBLES, first, f_res + (size_t)b * 12,
+                       ddq_res + (size_t)b * 6, H ? H + (size_t)b * 144 : nullptr, info + 4 * b);
+    __syncwarp();
+  }
+}
+
+// InvKin: four lanes per instance (one per foot), eight instances per warp
+__global__ void __launch_bounds__(128) invkin_kernel(const int B, const double* __restrict__ contacts,
+                                                     const double* __restrict__ goals,
+                                                     const double* __restrict__ vgoals,
+                                                     const double* __restrict__ agoals,
+                                                     const double* __restrict__ posf, const double* __restrict__ vf,
+                                                     const double* __restrict__ wf, const double* __restrict__ af,
+                                                     const double* __restrict__ Jf, double* ddq, double* dq_cmd,
+                                                     double* q_step) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = t >> 2, i = t & 3;
+  if (b >= B) return;
+  const double Kp = 100.0, Kd = 20.0;
+  double e[3], a[3], v[3], w[3], vg[3];
+  const size_t o12 = (size_t)b * 12;
+  for (int c = 0; c < 3; ++c) {
+    v[c] = vf[o12 + i + 4 * c];
+    w[c] = wf[o12 + i + 4 * c];
+    vg[c] = vgoals[o12 + c + 3 * i];
+    e[c] = goals[o12 + c + 3 * i] - posf[o12 + i + 4 * c];
+    a[c] = Kp * e[c] - Kd * (v[c] - vg[c]) + agoals[o12 + c + 3 * i];
+  }
+  if (contacts[(size_t)b * 4 + i] != 0.0)
+    for (int c = 0; c < 3; ++c) a[c] *= 0.0;
+  const double cr[3] = {w[1] * v[2] - w[2] * v[1], w[2] * v[0] - w[0] * v[2], w[0] * v[1] - w[1] * v[0]};
+  for (int c = 0; c < 3; ++c) a[c] -= af[o12 + i + 4 * c] + cr[c];
+  const double* J = Jf + (size_t)b * 144;
+  double Mm[3][3], I[3][3];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) Mm[r][c] = J[(3 * i + r) + 12 * (3 * i + c)];
+  const double c00 = Mm[1][1] * Mm[2][2] - Mm[1][2] * Mm[2][1];
+  const double c10 = Mm[1][2] * Mm[2][0] - Mm[1][0] * Mm[2][2];
+  const double c20 = Mm[1][0] * Mm[2][1] - Mm[1][1] * Mm[2][0];
+  const double det = c00 * Mm[0][0] + c10 * Mm[0][1] + c20 * Mm[0][2];
+  const double id = 1.0 / det;
+  I[0][0] = c00 * id;
+  I[1][0] = c10 * id;
+  I[2][0] = c20 * id;
+  I[0][1] = (Mm[0][2] * Mm[2][1] - Mm[0][1] * Mm[2][2]) * id;
+  I[1][1] = (Mm[0][0] * Mm[2][2] - Mm[0][2] * Mm[2][0]) * id;
+  I[2][1] = (Mm[0][1] * Mm[2][0] - Mm[0][0] * Mm[2][1]) * id;
+  I[0][2] = (Mm[0][1] * Mm[1][2] - Mm[0][2] * Mm[1][1]) * id;
+  I[1][2] = (Mm[0][2] * Mm[1][0] - Mm[0][0] * Mm[1][2]) * id;
+  I[2][2] = (Mm[0][0] * Mm[1][1] - Mm[0][1] * Mm[1][0]) * id;
+  for (int r = 0; r < 3; ++r) {
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int c = 0; c < 3; ++c) {
+      s0 += I[r][c] * a[c];
+      s1 += I[r][c] * vg[c];
+      s2 += I[r][c] * e[c];
+    }
+    ddq[o12 + 3 * i + r] = s0;
+    dq_cmd[o12 + 3 * i + r] = s1;
+    q_step[o12 + 3 * i + r] = s2;
+  }
+}
+
+// FP64 FMA peak: 8 independent DFMA chains per thread, 1024 threads per SM-slot
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double a, double b) {
+  double v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3, v4 = v0 + 4, v5 = v0 + 5, v6 = v0 + 6, v7 = v0 + 7;
+  for (int i = 0; i < iters; ++i) {
+    v0 = fma(v0, a, b);
+    v1 = fma(v1, a, b);
+    v2 = fma(v2, a, b);
+    v3 = fma(v3, a, b);
+    v4 = fma(v4, a, b);
+    v5 = fma(v5, a, b);
+    v6 = fma(v6, a, b);
+    v7 = fma(v7, a, b);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = ((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7));
+}
+
+int sm_count_of(int device) {
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
+  return n;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// handles
+// ------------------------------------------------------------------------------------------
+struct qrw_mpc {
+  int B, n_steps, N_gait, device, sms;
+  MpcConst C;
+  bool dbg_on = false;
+  double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
+         *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
+  int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr;
+  double *h_xref = nullptr, *h_fsteps = nullptr, *h_out = nullptr;  // pinned
+  cudaStream_t stream = nullptr;
+};
+struct qrw_wbc {
+  int B, device, sms;
+  WbcConst C;
+  bool first = true;
+  double *d_M = nullptr, *d_Jc = nullptr, *d_f = nullptr, *d_R = nullptr, *d_state = nullptr, *d_fres = nullptr,
+         *d_ddq = nullptr, *d_H = nullptr;
+  int *d_info = nullptr, *d_counter = nullptr;
+  cudaStream_t stream = nullptr;
+};
+
+extern "C" {
+
+const char* qrw_last_error(void) { return g_err.c_str(); }
+long long qrw_launch_count(void) { return g_launches; }
+int qrw_device_sm_count(int device, int* sm_count) {
+  int n = sm_count_of(device);
+  if (n <= 0) return fail("no usable CUDA device (this library has no CPU fallback)");
+  *sm_count = n;
+  return 0;
+}
+
+// Measured DFMA throughput of the device (the FP64 roofline denominator bench.py reports).
+int qrw_fp64_peak(int device, double* tflops) {
+  if (!tflops) return fail("qrw_fp64_peak: null argument");
+  const int sms = sm_count_of(device);
+  if (sms <= 0) return fail("qrw_fp64_peak: no usable CUDA device (this library has no CPU fallback)");
+  CU(cudaSetDevice(device));
+  const int blocks = sms * 8, iters = 1 << 14;
+  double* d = nullptr;
+  CU(cudaMalloc(&d, (size_t)blocks * 256 * sizeof(double)));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    CU(cudaEventRecord(e0));
+    fp64_peak_kernel<<<blocks, 256>>>(d, iters, 0.999999, 1e-9);
+    ++g_launches;
+    CU(cudaEventRecord(e1));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *tflops = 2.0 * 8.0 * (double)iters * 256.0 * blocks / (best * 1e-3) / 1e12;
+  return 0;
+}
+
+// ---------------------------------------------------------------- MPC
+int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_gait, int N_gait, int device) {
+  (void)T_gait;  // stored by the reference (MPC.cpp:6) but never read on this path
+  if (!out) return fail("qrw_mpc_create: null output handle");
+  if (batch <= 0) return fail("qrw_mpc_create: batch must be positive");
+  if (n_steps != NS) return fail("qrw_mpc_create: only n_steps == 16 is compiled in (src/config_solo12.yaml)");
+  if (N_gait <= n_steps || N_gait > NGMAX)
+    return fail("qrw_mpc_create: need n_steps < N_gait <= 32 (the reference writes gait.row(n_active))");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail("qrw_mpc_create: no CUDA device (this library has no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail("qrw_mpc_create: bad device index");
+  CU(cudaSetDevice(device));
+  auto* h = new qrw_mpc();
+  h->B = batch;
+  h->n_steps = n_steps;
+  h->N_gait = N_gait;
+  h->device = device;
+  h->sms = sm_count_of(device);
+  h->C = make_mpc_const(dt, N_gait);
+  const size_t B = (size_t)batch;
+  CU(cudaMalloc(&h->d_xref, B * 12 * (NS + 1) * sizeof(double)));
+  CU(cudaMalloc(&h->d_fsteps, B * 12 * N_gait * sizeof(double)));
+  CU(cudaMalloc(&h->d_out, B * 24 * NS * sizeof(double)));
+  CU(cudaMalloc(&h->d_state, B * MPC_STATE_DOUBLES * sizeof(double)));
+  CU(cudaMalloc(&h->d_state_i, B * MPC_STATE_INTS * sizeof(int)));
+  CU(cudaMalloc(&h->d_rho, B * sizeof(double)));
+  CU(cudaMalloc(&h->d_info, B * 4 * sizeof(int)));
+  CU(cudaMalloc(&h->d_counter, sizeof(int)));
+  CU(cudaMalloc(&h->d_gait, B * 4 * N_gait * sizeof(double)));
+  CU(cudaMalloc(&h->d_sgait, B * 12 * NS * sizeof(double)));
+  CU(cudaMemset(h->d_state, 0, B * MPC_STATE_DOUBLES * sizeof(double)));
+  CU(cudaMemset(h->d_state_i, 0, B * MPC_STATE_INTS * sizeof(int)));
+  CU(cudaMemset(h->d_out, 0, B * 24 * NS * sizeof(double)));
+  CU(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)));
+  CU(cudaMemset(h->d_rho, 0, B * sizeof(double)));
+  CU(cudaMallocHost(&h->h_xref, B * 12 * (NS + 1) * sizeof(double)));
+  CU(cudaMallocHost(&h->h_fsteps, B * 12 * N_gait * sizeof(double)));
+  CU(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)));
+  CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
+  *out = h;
+  return 0;
+}
+
+int qrw_mpc_destroy(qrw_mpc_t* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_xref);
+  cudaFree(h->d_fsteps);
+  cudaFree(h->d_out);
+  cudaFree(h->d_state);
+  cudaFree(h->d_state_i);
+  cudaFree(h->d_rho);
+  cudaFree(h->d_info);
+  cudaFree(h->d_counter);
+  cudaFree(h->d_gait);
+  cudaFree(h->d_sgait);
+  cudaFree(h->d_dbg);
+  cudaFreeHost(h->h_xref);
+  cudaFreeHost(h->h_fsteps);
+  cudaFreeHost(h->h_out);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const double* d_fsteps, void* stream) {
+  if (!h || !d_xref || !d_fsteps) return fail("qrw_mpc_run_device: null argument");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
+  int grid = 3 * h->sms;  // three 75 KB slabs per SM
+  if (grid > h->B) grid = h->B;
+  mpc_solve_kernel<<<grid, 32, MPC_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
+                                                    h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                    h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+  ++g_launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const double* fsteps) {
+  if (!h || !xref || !fsteps) return fail("qrw_mpc_run_host: null argument");
+  CU(cudaSetDevice(h->device));
+  const size_t B = (size_t)h->B;
+  CU(cudaMemcpyAsync(h->d_xref, xref, B * 12 * (NS + 1) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_fsteps, fsteps, B * 12 * h->N_gait * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  if (qrw_mpc_run_device(h, num_iter, h->d_xref, h->d_fsteps, h->stream)) return 1;
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int qrw_mpc_result_host(qrw_mpc_t* h, double* out) {
+  if (!h || !out) return fail("qrw_mpc_result_host: null argument");
+  CU(cudaSetDevice(h->device));
+  CU(cudaMemcpyAsync(out, h->d_out, (size_t)h->B * 24 * NS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int qrw_mpc_result_device(qrw_mpc_t* h, const double** d_out) {
+  if (!h || !d_out) return fail("qrw_mpc_result_device: null argument");
+  *d_out = h->d_out;
+  return 0;
+}
+
+static int mpc_unpack(qrw_mpc_t* h) {
+  const int per = 4 * h->N_gait + 12 * NS;
+  const long long total = (long long)h->B * per;
+  mpc_unpack_gait_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(h->d_state_i, h->B, h->N_gait,
+                                                                                h->d_gait, h->d_sgait);
+  ++g_launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+int qrw_mpc_gait_host(qrw_mpc_t* h, double* out) {
+  if (!h || !out) return fail("qrw_mpc_gait_host: null argument");
+  CU(cudaSetDevice(h->device));
+  if (mpc_unpack(h)) return 1;
+  CU(cudaMemcpyAsync(out, h->d_gait, (size_t)h->B * 4 * h->N_gait * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int qrw_mpc_sgait_host(qrw_mpc_t* h, double* out) {
+  if (!h || !out) return fail("qrw_mpc_sgait_host: null argument");
+  CU(cudaSetDevice(h->device));
+  if (mpc_unpack(h)) return 1;
+  CU(cudaMemcpyAsync(out, h->d_sgait, (size_t)h->B * 12 * NS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int qrw_mpc_info_host(qrw_mpc_t* h, int* iters, int* status, double* rho, int* n_factor) {
+  if (!h) return fail("qrw_mpc_info_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  int* tmp = new int[(size_t)h->B * 4];
+  cudaError_t e = cudaMemcpy(tmp, h->d_info, (size_t)h->B * 4 * sizeof(int), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && rho) e = cudaMemcpy(rho, h->d_rho, (size_t)h->B * sizeof(double), cudaMemcpyDeviceToHost);
+  for (int b = 0; b < h->B; ++b) {
+    if (iters) iters[b] = tmp[4 * b];
+    if (status) status[b] = tmp[4 * b + 1];
+    if (n_factor) n_factor[b] = tmp[4 * b + 2];
+  }
+  delete[] tmp;
+  if (e != cudaSuccess) return fail(std::string("qrw_mpc_info_host: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
+  if (!h) return fail("qrw_mpc_set_max_iter: null handle");
+  if (max_iter <= 0 || max_iter % h->C.check_every != 0)
+    return fail("qrw_mpc_set_max_iter: max_iter must be a positive multiple of 25 (check_termination)");
+  h->C.max_iter = max_iter;
+  return 0;
+}
+int qrw_mpc_debug_host(qrw_mpc_t* h, double* out) {
+  if (!h) return fail("qrw_mpc_debug_host: null handle");
+  CU(cudaSetDevice(h->device));
+  if (!h->d_dbg) {
+    CU(cudaMalloc(&h->d_dbg, (size_t)h->B * 1281 * sizeof(double)));
+    CU(cudaMemset(h->d_dbg, 0, (size_t)h->B * 1281 * sizeof(double)));
+  }
+  h->dbg_on = true;
+  if (out) {
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(out, h->d_dbg, (size_t)h->B * 1281 * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
+int qrw_mpc_state_bytes(qrw_mpc_t* h, size_t* bytes) {
+  if (!h || !bytes) return fail("qrw_mpc_state_bytes: null argument");
+  *bytes = (size_t)h->B * (MPC_STATE_DOUBLES * sizeof(double) + MPC_STATE_INTS * sizeof(int));
+  return 0;
+}
+int qrw_mpc_state_save(qrw_mpc_t* h, void* d_buf, void* stream) {
+  if (!h || !d_buf) return fail("qrw_mpc_state_save: null argument");
+  CU(cudaSetDevice(h->device));
+  const size_t nd = (size_t)h->B * MPC_STATE_DOUBLES * sizeof(double), ni = (size_t)h->B * MPC_STATE_INTS * sizeof(int);
+  CU(cudaMemcpyAsync(d_buf, h->d_state, nd, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  CU(cudaMemcpyAsync((char*)d_buf + nd, h->d_state_i, ni, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+int qrw_mpc_state_load(qrw_mpc_t* h, const void* d_buf, void* stream) {
+  if (!h || !d_buf) return fail("qrw_mpc_state_load: null argument");
+  CU(cudaSetDevice(h->device));
+  const size_t nd = (size_t)h->B * MPC_STATE_DOUBLES * sizeof(double), ni = (size_t)h->B * MPC_STATE_INTS * sizeof(int);
+  CU(cudaMemcpyAsync(h->d_state, d_buf, nd, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  CU(cudaMemcpyAsync(h->d_state_i, (const char*)d_buf + nd, ni, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+int qrw_mpc_pinned(qrw_mpc_t* h, double** xref, double** fsteps, double** result) {
+  if (!h) return fail("qrw_mpc_pinned: null handle");
+  if (xref) *xref = h->h_xref;
+  if (fsteps) *fsteps = h->h_fsteps;
+  if (result) *result = h->h_out;
+  return 0;
+}
+
+// ---------------------------------------------------------------- QPWBC
+int qrw_wbc_create(qrw_wbc_t** out, int batch, int device) {
+  if (!out) return fail("qrw_wbc_create: null output handle");
+  if (batch <= 0) return fail("qrw_wbc_create: batch must be positive");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail("qrw_wbc_create: no CUDA device (this library has no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail("qrw_wbc_create: bad device index");
+  CU(cudaSetDevice(device));
+  auto* h = new qrw_wbc();
+  h->B = batch;
+  h->device = device;
+  h->sms = sm_count_of(device);
+  h->C = make_wbc_const();
+  const size_t B = (size_t)batch;
+  CU(cudaMalloc(&h->d_M, B * 324 * sizeof(double)));
+  CU(cudaMalloc(&h->d_Jc, B * 216 * sizeof(double)));
+  CU(cudaMalloc(&h->d_f, B * 12 * sizeof(double)));
+  CU(cudaMalloc(&h->d_R, B * 6 * sizeof(double)));
+  CU(cudaMalloc(&h->d_state, B * WBC_STATE_DOUBLES * sizeof(double)));
+  CU(cudaMalloc(&h->d_fres, B * 12 * sizeof(double)));
+  CU(cudaMalloc(&h->d_ddq, B * 6 * sizeof(double)));
+  CU(cudaMalloc(&h->d_H, B * 144 * sizeof(double)));
+  CU(cudaMalloc(&h->d_info, B * 4 * sizeof(int)));
+  CU(cudaMalloc(&h->d_counter, sizeof(int)));
+  CU(cudaMemset(h->d_state, 0, B * WBC_STATE_DOUBLES * sizeof(double)));
+  CU(cudaMemset(h->d_fres, 0, B * 12 * sizeof(double)));
+  CU(cudaMemset(h->d_ddq, 0, B * 6 * sizeof(double)));
+  CU(cudaMemset(h->d_H, 0, B * 144 * sizeof(double)));
+  CU(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)));
+  CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  *out = h;
+  return 0;
+}
+int qrw_wbc_destroy(qrw_wbc_t* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_M);
+  cudaFree(h->d_Jc);
+  cudaFree(h->d_f);
+  cudaFree(h->d_R);
+  cudaFree(h->d_state);
+  cudaFree(h->d_fres);
+  cudaFree(h->d_ddq);
+  cudaFree(h->d_H);
+  cudaFree(h->d_info);
+  cudaFree(h->d_counter);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+int qrw_wbc_run_device(qrw_wbc_t* h, const double* d_M, const double* d_Jc, const double* d_f_cmd,
+                       const double* d_RNEA, void* stream) {
+  if (!h || !d_M || !d_Jc || !d_f_cmd || !d_RNEA) return fail("qrw_wbc_run_device: null argument");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
+  int grid = 7 * h->sms;  // 7 CTAs x 4 warps x 7.9 KB per SM
+  const int need = (h->B + WBC_WARPS - 1) / WBC_WARPS;
+  if (grid > need) grid = need;
+  wbc_solve_kernel<<<grid, 32 * WBC_WARPS, WBC_WARPS * WBC_SLAB_BYTES, s>>>(
+      h->C, h->B, h->first ? 1 : 0, d_M, d_Jc, d_f_cmd, d_RNEA, h->d_state, h->d_fres, h->d_ddq, h->d_H, h->d_info,
+      h->d_counter);
+  ++g_launches;
+  CU(cudaGetLastError());
+  h->first = false;  // QPWBC::initialized, src/QPWBC.cpp:23,254
+  return 0;
+}
+int qrw_wbc_run_host(qrw_wbc_t* h, const double* M, const double* Jc, const double* f_cmd, const double* RNEA) {
+  if (!h || !M || !Jc || !f_cmd || !RNEA) return fail("qrw_wbc_run_host: null argument");
+  CU(cudaSetDevice(h->device));
+  const size_t B = (size_t)h->B;
+  CU(cudaMemcpyAsync(h->d_M, M, B * 324 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_Jc, Jc, B * 216 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_f, f_cmd, B * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_R, RNEA, B * 6 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  if (qrw_wbc_run_device(h, h->d_M, h->d_Jc, h->d_f, h->d_R, h->stream)) return 1;
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int qrw_wbc_result_host(qrw_wbc_t* h, double* f_res, double* ddq_res, double* H) {
+  if (!h) return fail("qrw_wbc_result_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  const size_t B = (size_t)h->B;
+  if (f_res) CU(cudaMemcpy(f_res, h->d_fres, B * 12 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (ddq_res) CU(cudaMemcpy(ddq_res, h->d_ddq, B * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (H) CU(cudaMemcpy(H, h->d_H, B * 144 * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+int qrw_wbc_result_device(qrw_wbc_t* h, const double** d_f_res, const double** d_ddq_res) {
+  if (!h) return fail("qrw_wbc_result_device: null handle");
+  if (d_f_res) *d_f_res = h->d_fres;
+  if (d_ddq_res) *d_ddq_res = h->d_ddq;
+  return 0;
+}
+int qrw_wbc_info_host(qrw_wbc_t* h, int* iters, int* status, double* rho) {
+  if (!h) return fail("qrw_wbc_info_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  const size_t B = (size_t)h->B;
+  int* tmp = new int[B * 4];
+  double* st = rho ? new double[B * WBC_STATE_DOUBLES] : nullptr;
+  cudaError_t e = cudaMemcpy(tmp, h->d_info, B * 4 * sizeof(int), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && rho) e = cudaMemcpy(st, h->d_state, B * WBC_STATE_DOUBLES * sizeof(double), cudaMemcpyDeviceToHost);
+  for (size_t b = 0; b < B; ++b) {
+    if (iters) iters[b] = tmp[4 * b];
+    if (status) status[b] = tmp[4 * b + 1];
+    if (rho) rho[b] = st[b * WBC_STATE_DOUBLES + WS_RHO];
+  }
+  delete[] tmp;
+  delete[] st;
+  if (e != cudaSuccess) return fail(std::string("qrw_wbc_info_host: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+// ---------------------------------------------------------------- InvKin
+int qrw_invkin_run_device(int batch, const double* contacts, const double* goals, const double* vgoals,
+                          const double* agoals, const double* posf, const double* vf, const double* wf,
+                          const double* af, const double* Jf, double* ddq, double* dq_cmd, double* q_step,
+                          void* stream) {
+  if (batch <= 0) return fail("qrw_invkin_run_device: batch must be positive");
+  if (!contacts || !goals || !vgoals || !agoals || !posf || !vf || !wf || !af || !Jf || !ddq || !dq_cmd || !q_step)
+    return fail("qrw_invkin_run_device: null argument");
+  const long long threads = 4LL * batch;
+  invkin_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      batch, contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf, ddq, dq_cmd, q_step);
+  ++g_launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+int qrw_invkin_run_host(int batch, const double* contacts, const double* goals, const double* vgoals,
+                        const double* agoals, const double* posf, const double* vf, const double* wf,
+                        const double* af, const double* Jf, double* ddq, double* dq_cmd, double* q_step) {
+  if (batch <= 0) return fail("qrw_invkin_run_host: batch must be positive");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail("qrw_invkin_run_host: no CUDA device (this library has no CPU fallback)");
+  const size_t B = (size_t)batch;
+  const size_t in_sz[9] = {4, 12, 12, 12, 12, 12, 12, 12, 144};
+  const double* in_h[9] = {contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf};
+  double* in_d[9] = {nullptr};
+  double* out_d[3] = {nullptr};
+  double* out_h[3] = {ddq, dq_cmd, q_step};
+  int rc = 0;
+  for (int i = 0; i < 9 && !rc; ++i) {
+    if (cudaMalloc(&in_d[i], B * in_sz[i] * sizeof(double)) != cudaSuccess ||
+        cudaMemcpy(in_d[i], in_h[i], B * in_sz[i] * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess)
+      rc = fail("qrw_invkin_run_host: allocation / H2D copy failed");
+  }
+  for (int i = 0; i < 3 && !rc; ++i)
+    if (cudaMalloc(&out_d[i], B * 12 * sizeof(double)) != cudaSuccess) rc = fail("qrw_invkin_run_host: allocation failed");
+  if (!rc)
+    rc = qrw_invkin_run_device(batch, in_d[0], in_d[1], in_d[2], in_d[3], in_d[4], in_d[5], in_d[6], in_d[7], in_d[8],
+                               out_d[0], out_d[1], out_d[2], nullptr);
+  for (int i = 0; i < 3 && !rc; ++i)
+    if (cudaMemcpy(out_h[i], out_d[i], B * 12 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess)
+      rc = fail("qrw_invkin_run_host: D2H copy failed");
+  for (int i = 0; i < 9; ++i) cudaFree(in_d[i]);
+  for (int i = 0; i < 3; ++i) cudaFree(out_d[i]);
+  return rc;
+}
+
+}  // extern "C"

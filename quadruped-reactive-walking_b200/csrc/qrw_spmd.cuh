@@ -34,6 +34,12 @@ namespace qrw {
 QRW_HD double dmax(double a, double b) { return a > b ? a : b; }
 QRW_HD double dmin(double a, double b) { return a < b ? a : b; }
 
+// OSQP limit_scaling (scaling.c): MIN_SCALING 1e-4 -> 1, MAX_SCALING 1e4
+QRW_HD double limit_scaling(double v) {
+  v = v < 1e-4 ? 1.0 : v;
+  return v > 1e4 ? 1e4 : v;
+}
+
 // max over the 32 per-lane partials red[0..31] (uniform code; callers sync before and after)
 QRW_HD double red_max32(const double* red) {
   double m = red[0];

@@ -1,0 +1,102 @@
+"""ctypes loader for libqrw_b200.so (built in-tree by __graft_entry__.build())."""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+_CSRC = os.path.join(_ROOT, "csrc")
+_SO = os.path.join(_ROOT, "libqrw_b200.so")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
+              "-Xcompiler", "-fPIC"]
+
+
+class QrwError(RuntimeError):
+    """An entry point of libqrw_b200.so returned non-zero (text from qrw_last_error())."""
+
+
+def library_path():
+    return _SO
+
+
+def _stale():
+    if not os.path.exists(_SO):
+        return True
+    t = os.path.getmtime(_SO)
+    srcs = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)] + [os.path.join(os.path.dirname(_ROOT), "include", "qrw_b200.h")]
+    return any(os.path.getmtime(s) > t for s in srcs if os.path.exists(s))
+
+
+def build_library(force=False, verbose=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a ... (cross-compiles without a GPU)."""
+    if not force and not _stale():
+        return _SO
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", _SO, os.path.join(_CSRC, "qrw_b200.cu")]
+    subprocess.check_call(cmd)
+    return _SO
+
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_vp = C.c_void_p
+_lib = None
+
+_SIGNATURES = {
+    "qrw_last_error": (C.c_char_p, []),
+    "qrw_launch_count": (C.c_longlong, []),
+    "qrw_device_sm_count": (C.c_int, [C.c_int, _ip]),
+    "qrw_fp64_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
+    "qrw_mpc_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int]),
+    "qrw_mpc_destroy": (C.c_int, [_vp]),
+    "qrw_mpc_run_device": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
+    "qrw_mpc_run_host": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "qrw_mpc_result_host": (C.c_int, [_vp, _vp]),
+    "qrw_mpc_result_device": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "qrw_mpc_gait_host": (C.c_int, [_vp, _vp]),
+    "qrw_mpc_sgait_host": (C.c_int, [_vp, _vp]),
+    "qrw_mpc_info_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "qrw_mpc_set_max_iter": (C.c_int, [_vp, C.c_int]),
+    "qrw_mpc_debug_host": (C.c_int, [_vp, _vp]),
+    "qrw_mpc_state_bytes": (C.c_int, [_vp, C.POINTER(C.c_size_t)]),
+    "qrw_mpc_state_save": (C.c_int, [_vp, _vp, _vp]),
+    "qrw_mpc_state_load": (C.c_int, [_vp, _vp, _vp]),
+    "qrw_mpc_pinned": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "qrw_wbc_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int]),
+    "qrw_wbc_destroy": (C.c_int, [_vp]),
+    "qrw_wbc_run_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "qrw_wbc_run_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "qrw_wbc_result_host": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "qrw_wbc_result_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
+    "qrw_wbc_info_host": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "qrw_invkin_run_device": (C.c_int, [C.c_int] + [_vp] * 13),
+    "qrw_invkin_run_host": (C.c_int, [C.c_int] + [_vp] * 12),
+}
+
+
+def exported_symbols():
+    """Names the ctypes layer binds -- tests compare this list with include/qrw_b200.h."""
+    return sorted(_SIGNATURES)
+
+
+def load_library():
+    """Load libqrw_b200.so; raises QrwError (never falls back) if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise QrwError(
+                f"{_SO} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()'). "
+                "qrw_b200 has no CPU fallback.")
+        L = C.CDLL(_SO)
+        for name, (res, args) in _SIGNATURES.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise QrwError(load_library().qrw_last_error().decode() or f"error code {rc}")

@@ -1,0 +1,245 @@
+"""Batched solver objects over the C ABI (include/qrw_b200.h).
+
+Arrays are in the ABI layout: instance-major, column-major inside an instance (what
+``Eigen::MatrixXd::data()`` holds in the reference).  ``pack_cols`` converts a stack of natural
+``[B, rows, cols]`` numpy matrices.  Host inputs (numpy) go through the ``*_host`` entry points
+(H2D/D2H inside the call); CUDA tensors (torch) go through the ``*_device`` entry points and stay
+asynchronous on the current torch stream.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import check, load_library
+
+N_STEPS = 16
+
+
+def pack_cols(mats):
+    """[B, r, c] natural indexing -> [B, r*c] column-major per instance."""
+    mats = np.asarray(mats, dtype=np.float64)
+    return np.ascontiguousarray(mats.transpose(0, 2, 1)).reshape(mats.shape[0], -1)
+
+
+def unpack_cols(flat, rows, cols):
+    """[B, r*c] column-major per instance -> [B, r, c]."""
+    flat = np.asarray(flat)
+    return flat.reshape(flat.shape[0], cols, rows).transpose(0, 2, 1)
+
+
+def _is_cuda_tensor(a):
+    return hasattr(a, "is_cuda") and a.is_cuda
+
+
+def _host(a, n):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if a.size != n:
+        raise ValueError(f"expected {n} doubles, got {a.size}")
+    return a
+
+
+def _dev_ptr(t, n):
+    import torch
+
+    if t.dtype != torch.float64 or not t.is_contiguous() or t.numel() != n:
+        raise ValueError(f"expected a contiguous float64 CUDA tensor with {n} elements")
+    return C.c_void_p(t.data_ptr())
+
+
+def _torch_stream():
+    import torch
+
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _DevView:
+    """Expose a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f8", "data": (int(ptr), False), "version": 2}
+
+
+class BatchedMPC:
+    """B independent ``MPC`` objects (reference src/MPC.cpp) on one GPU.
+
+    run(num_iter, xref, fsteps) / get_latest_result() / get_gait() / get_Sgait() keep the reference
+    names (python/gepadd.cpp:22-31); xref is [B, 12*(n+1)], fsteps [B, N_gait*12], result [B, 24*n].
+    """
+
+    def __init__(self, batch, dt=0.02, n_steps=N_STEPS, T_gait=0.32, N_gait=20, device=0):
+        self._L = load_library()
+        self.B, self.n, self.N_gait, self.device = int(batch), int(n_steps), int(N_gait), int(device)
+        h = C.c_void_p()
+        check(self._L.qrw_mpc_create(C.byref(h), self.B, float(dt), self.n, float(T_gait), self.N_gait, self.device))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.qrw_mpc_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # -- reference-named API
+    def run(self, num_iter, xref, fsteps):
+        nx, nf = self.B * 12 * (self.n + 1), self.B * 12 * self.N_gait
+        if _is_cuda_tensor(xref):
+            check(self._L.qrw_mpc_run_device(self._h, int(num_iter), _dev_ptr(xref, nx), _dev_ptr(fsteps, nf), _torch_stream()))
+        else:
+            x, f = _host(xref, nx), _host(fsteps, nf)
+            check(self._L.qrw_mpc_run_host(self._h, int(num_iter), x.ctypes.data, f.ctypes.data))
+        return 0
+
+    def get_latest_result(self, out=None):
+        if out is None:
+            out = np.empty((self.B, 24 * self.n))
+        elif out.dtype != np.float64 or not out.flags.c_contiguous or out.size != self.B * 24 * self.n:
+            raise ValueError("out must be a contiguous float64 array of B*24*n elements")
+        check(self._L.qrw_mpc_result_host(self._h, out.ctypes.data))
+        return out
+
+    def get_gait(self):
+        out = np.empty((self.B, 4 * self.N_gait))
+        check(self._L.qrw_mpc_gait_host(self._h, out.ctypes.data))
+        return out
+
+    def get_Sgait(self):
+        out = np.empty((self.B, 12 * self.n))
+        check(self._L.qrw_mpc_sgait_host(self._h, out.ctypes.data))
+        return out
+
+    # -- batched extras
+    def result_tensor(self):
+        """Zero-copy torch view [B, 24*n] of the device result buffer."""
+        import torch
+
+        p = C.c_void_p()
+        check(self._L.qrw_mpc_result_device(self._h, C.byref(p)))
+        return torch.as_tensor(_DevView(p.value, (self.B, 24 * self.n)), device=f"cuda:{self.device}")
+
+    def info(self):
+        it = np.empty(self.B, np.int32)
+        st = np.empty(self.B, np.int32)
+        rho = np.empty(self.B)
+        nf = np.empty(self.B, np.int32)
+        check(self._L.qrw_mpc_info_host(self._h, it.ctypes.data, st.ctypes.data, rho.ctypes.data, nf.ctypes.data))
+        return dict(iters=it, status=st, rho=rho, n_factor=nf)
+
+    def set_max_iter(self, k):
+        check(self._L.qrw_mpc_set_max_iter(self._h, int(k)))
+
+    def enable_debug(self):
+        check(self._L.qrw_mpc_debug_host(self._h, None))
+
+    def debug(self):
+        out = np.empty((self.B, 1281))
+        check(self._L.qrw_mpc_debug_host(self._h, out.ctypes.data))
+        return dict(D=out[:, :384], E=out[:, 384:1088], c=out[:, 1088], bounds=out[:, 1089:])
+
+    def state_bytes(self):
+        n = C.c_size_t()
+        check(self._L.qrw_mpc_state_bytes(self._h, C.byref(n)))
+        return n.value
+
+    def state_save(self, buf):
+        """buf: torch uint8 CUDA tensor of state_bytes()."""
+        check(self._L.qrw_mpc_state_save(self._h, C.c_void_p(buf.data_ptr()), _torch_stream()))
+
+    def state_load(self, buf):
+        check(self._L.qrw_mpc_state_load(self._h, C.c_void_p(buf.data_ptr()), _torch_stream()))
+
+    def pinned(self):
+        """numpy views of the handle's pinned staging buffers (xref, fsteps, result)."""
+        px, pf, pr = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(self._L.qrw_mpc_pinned(self._h, C.byref(px), C.byref(pf), C.byref(pr)))
+
+        def view(p, n):
+            return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(n,))
+
+        return (view(px, self.B * 12 * (self.n + 1)).reshape(self.B, -1), view(pf, self.B * 12 * self.N_gait).reshape(self.B, -1),
+                view(pr, self.B * 24 * self.n).reshape(self.B, -1))
+
+
+class BatchedQPWBC:
+    """B independent ``QPWBC`` objects (reference src/QPWBC.cpp).  run(M, Jc, f_cmd, RNEA) with
+    M [B, 324], Jc [B, 216] (column-major 18x18 / 12x18), f_cmd [B, 12], RNEA [B, 6]."""
+
+    def __init__(self, batch, device=0):
+        self._L = load_library()
+        self.B, self.device = int(batch), int(device)
+        h = C.c_void_p()
+        check(self._L.qrw_wbc_create(C.byref(h), self.B, self.device))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.qrw_wbc_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def run(self, M, Jc, f_cmd, RNEA, k_contacts=None):
+        B = self.B
+        if _is_cuda_tensor(M):
+            check(self._L.qrw_wbc_run_device(self._h, _dev_ptr(M, B * 324), _dev_ptr(Jc, B * 216), _dev_ptr(f_cmd, B * 12),
+                                             _dev_ptr(RNEA, B * 6), _torch_stream()))
+        else:
+            a = [_host(M, B * 324), _host(Jc, B * 216), _host(f_cmd, B * 12), _host(RNEA, B * 6)]
+            check(self._L.qrw_wbc_run_host(self._h, *[x.ctypes.data for x in a]))
+        return 0
+
+    compute = run  # north-star alias
+
+    def results(self, with_H=True):
+        f, d = np.empty((self.B, 12)), np.empty((self.B, 6))
+        H = np.empty((self.B, 144)) if with_H else None
+        check(self._L.qrw_wbc_result_host(self._h, f.ctypes.data, d.ctypes.data, H.ctypes.data if with_H else None))
+        return f, d, H
+
+    def get_f_res(self):
+        return self.results(False)[0]
+
+    def get_ddq_res(self):
+        return self.results(False)[1]
+
+    def get_H(self):
+        return self.results(True)[2]
+
+    def info(self):
+        it = np.empty(self.B, np.int32)
+        st = np.empty(self.B, np.int32)
+        rho = np.empty(self.B)
+        check(self._L.qrw_wbc_info_host(self._h, it.ctypes.data, st.ctypes.data, rho.ctypes.data))
+        return dict(iters=it, status=st, rho=rho)
+
+
+class BatchedInvKin:
+    """Batched ``InvKin::refreshAndCompute`` (reference src/InvKin.cpp:23-73); stateless."""
+
+    def __init__(self, batch, device=0):
+        self._L = load_library()
+        self.B = int(batch)
+        self.ddq = self.dq_cmd = self.q_step = None
+
+    def refreshAndCompute(self, contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf):
+        B = self.B
+        sizes = [4, 12, 12, 12, 12, 12, 12, 12, 144]
+        args = [contacts, goals, vgoals, agoals, posf, vf, wf, af, Jf]
+        if _is_cuda_tensor(contacts):
+            import torch
+
+            outs = [torch.empty(B, 12, dtype=torch.float64, device=contacts.device) for _ in range(3)]
+            check(self._L.qrw_invkin_run_device(B, *[_dev_ptr(a, B * s) for a, s in zip(args, sizes)],
+                                                *[C.c_void_p(o.data_ptr()) for o in outs], _torch_stream()))
+        else:
+            a = [_host(x, B * s) for x, s in zip(args, sizes)]
+            outs = [np.empty((B, 12)) for _ in range(3)]
+            check(self._L.qrw_invkin_run_host(B, *[x.ctypes.data for x in a], *[o.ctypes.data for o in outs]))
+        self.ddq, self.dq_cmd, self.q_step = outs
+        return self.ddq
+
+    def get_q_step(self):
+        return self.q_step
+
+    def get_dq_cmd(self):
+        return self.dq_cmd

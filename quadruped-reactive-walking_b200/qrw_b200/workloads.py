@@ -26,6 +26,13 @@ SHOULDERS = np.array([[0.1946, 0.1946, -0.1946, -0.1946], [0.14695, -0.14695, 0.
 
 GAITS = ("trot", "walk", "bounding", "pacing", "static")
 
+# Algorithmic FP64 work of the block-tridiagonal ADMM (DESIGN.md "FLOP model"): per iteration 16 dense
+# 24x24 mat-vecs (forward) + 15 dense 24x12 (backward) + two passes over the 1998-nnz constraint
+# matrix + ~10 vector ops on 704 rows and 6 on 384 variables; per call 16 Gauss-Jordan 24^3
+# inversions with their block assembly and 10 Ruiz passes.
+FLOP_PER_ADMM_ITER = 16 * 2 * 576 + 15 * 2 * 288 + 4 * 1998 + 10 * 704 + 6 * 384
+FLOP_PER_SETUP = 16 * (2 * 24 ** 3 + 12000) + 10 * 12000
+
 
 def gait_cycle(name, n=N_STEPS):
     """One period (n rows x 4) of the named gait, rows of 0/1 (Gait.cpp:38-108)."""
@@ -162,3 +169,82 @@ def four_stance(x0=None):
 def next_state(result, n=N_STEPS):
     """Predicted next state x_f_applied[:12, 0] of every instance: result is [B, 24*n]."""
     return result[:, :12].copy()
+
+
+# ---------------------------------------------------------------------------------------------
+# QPWBC / InvKin drop-in API inputs (matrices as scripts/QP_WBC.py:88-107 and
+# scripts/solo12InvKin.py:47-62 hand them to the C++ classes), synthetic.
+# ---------------------------------------------------------------------------------------------
+MASS = 2.500002861022949  # (double)2.50000279f, src/MPC.cpp:17
+Y_DIAG = np.array([MASS, MASS, MASS, 0.0309249, 0.051061, 0.0693976])  # composite body at q = 0
+
+
+def _skew(v):
+    z = np.zeros(v.shape[:-1])
+    return np.stack([np.stack([z, -v[..., 2], v[..., 1]], -1), np.stack([v[..., 2], z, -v[..., 0]], -1),
+                     np.stack([-v[..., 1], v[..., 0], z], -1)], -2)
+
+
+def wbc_inputs(B, seed, swing_prob=0.35):
+    """(M [B,324], Jc [B,216], f_cmd [B,12], RNEA [B,6]) in the C-ABI layout.
+
+    M: 18x18 with the 6x6 base block masked to its diagonal (scripts/QP_WBC.py:89-93); Jc rows of a
+    stance foot = [I3 | -skew(p_foot) | leg block], zero for swing feet (:96-101); f_cmd = weight
+    shared by the stance feet plus noise inside the friction cone, 0 for swing feet; RNEA = base
+    wrench of a slowly moving trunk.
+    """
+    rng = np.random.default_rng(seed)
+    M = np.zeros((B, 18, 18))
+    M[:, np.arange(6), np.arange(6)] = Y_DIAG
+    L = rng.uniform(-0.02, 0.02, (B, 12, 12))
+    M[:, 6:, 6:] = np.einsum("bij,bkj->bik", L, L) + 0.01 * np.eye(12)
+    M[:, :6, 6:] = rng.uniform(-0.02, 0.02, (B, 6, 12))
+    M[:, 6:, :6] = M[:, :6, 6:].transpose(0, 2, 1)
+    contact = rng.uniform(size=(B, 4)) > swing_prob
+    contact[contact.sum(1) == 0, 0] = True
+    p = np.zeros((B, 4, 3))
+    p[..., 0] = SHOULDERS[0] + rng.uniform(-0.05, 0.05, (B, 4))
+    p[..., 1] = SHOULDERS[1] + rng.uniform(-0.05, 0.05, (B, 4))
+    p[..., 2] = -rng.uniform(0.18, 0.26, (B, 1))
+    Jc = np.zeros((B, 12, 18))
+    for i in range(4):
+        Jc[:, 3 * i:3 * i + 3, 0:3] = np.eye(3)
+        Jc[:, 3 * i:3 * i + 3, 3:6] = -_skew(p[:, i])
+        Jc[:, 3 * i:3 * i + 3, 6 + 3 * i:9 + 3 * i] = rng.uniform(-0.2, 0.2, (B, 3, 3))
+    Jc *= np.repeat(contact, 3, axis=1)[:, :, None]
+    nc = contact.sum(1, keepdims=True)
+    f = np.zeros((B, 4, 3))
+    f[..., 2] = MASS * 9.81 / nc + rng.uniform(-1.0, 1.0, (B, 4))
+    f[..., 0:2] = rng.uniform(-0.3, 0.3, (B, 4, 2)) * f[..., 2:3]
+    f *= contact[..., None]
+    RNEA = np.zeros((B, 6))
+    RNEA[:, 2] = MASS * 9.81
+    RNEA += rng.uniform(-1.0, 1.0, (B, 6)) * np.array([2.0, 2.0, 2.0, 0.3, 0.3, 0.3])
+    return pack_cols(M), pack_cols(Jc), f.reshape(B, 12), RNEA
+
+
+def pack_cols(mats):
+    mats = np.asarray(mats, dtype=np.float64)
+    return np.ascontiguousarray(mats.transpose(0, 2, 1)).reshape(mats.shape[0], -1)
+
+
+def invkin_inputs(B, seed):
+    """(contacts [B,4], goals, vgoals, agoals [B,12] (3x4 col-major), posf, vf, wf, af [B,12]
+    (4x3 col-major), Jf [B,144] (12x12 col-major)) for InvKin::refreshAndCompute."""
+    rng = np.random.default_rng(seed)
+    contacts = (rng.uniform(size=(B, 4)) > 0.4).astype(np.float64)
+    posf = np.zeros((B, 4, 3))
+    posf[..., 0] = SHOULDERS[0] + rng.uniform(-0.03, 0.03, (B, 4))
+    posf[..., 1] = SHOULDERS[1] + rng.uniform(-0.03, 0.03, (B, 4))
+    posf[..., 2] = -0.22 + rng.uniform(-0.03, 0.03, (B, 4))
+    goals = posf.transpose(0, 2, 1) + rng.uniform(-0.03, 0.03, (B, 3, 4))
+    vgoals = rng.uniform(-0.5, 0.5, (B, 3, 4))
+    agoals = rng.uniform(-5.0, 5.0, (B, 3, 4))
+    vf = rng.uniform(-0.5, 0.5, (B, 4, 3))
+    wf = rng.uniform(-2.0, 2.0, (B, 4, 3))
+    af = rng.uniform(-3.0, 3.0, (B, 4, 3))
+    Jf = rng.uniform(-0.05, 0.05, (B, 12, 12))
+    for i in range(4):  # well-conditioned diagonal 3x3 leg blocks
+        Jf[:, 3 * i:3 * i + 3, 3 * i:3 * i + 3] += 0.16 * np.eye(3) + rng.uniform(-0.08, 0.08, (B, 3, 3))
+    return (contacts, pack_cols(goals), pack_cols(vgoals), pack_cols(agoals), pack_cols(posf), pack_cols(vf),
+            pack_cols(wf), pack_cols(af), pack_cols(Jf))

@@ -38,3 +38,24 @@ void emu_mpc_run(int B, double dt, int N_gait, int first, int max_iter, const do
   }
 }
 }
+
+#include "../../quadruped-reactive-walking_b200/csrc/wbc_core.cuh"
+extern "C" {
+int emu_wbc_state_doubles() { return WBC_STATE_DOUBLES; }
+void emu_wbc_run(int B, int first, const double* M, const double* Jc, const double* f_cmd, const double* RNEA,
+                 double* st, double* f_res, double* ddq_res, double* H, int* info) {
+  WbcConst C = make_wbc_const();
+  std::vector<double> slab(WBC_SLAB_DOUBLES, 0.0);
+  for (int b = 0; b < B; ++b)
+    wbc_solve_instance(C, slab.data(), M + (size_t)b * 324, Jc + (size_t)b * 216, f_cmd + 12 * b, RNEA + 6 * b,
+                       st + (size_t)b * WBC_STATE_DOUBLES, first, f_res + 12 * b, ddq_res + 6 * b,
+                       H ? H + 144 * b : nullptr, info + 4 * b);
+}
+void emu_invkin_run(int B, const double* contacts, const double* goals, const double* vgoals, const double* agoals,
+                    const double* posf, const double* vf, const double* wf, const double* af, const double* Jf,
+                    double* ddq, double* dq_cmd, double* q_step) {
+  for (int b = 0; b < B; ++b)
+    invkin_instance(contacts + 4 * b, goals + 12 * b, vgoals + 12 * b, agoals + 12 * b, posf + 12 * b, vf + 12 * b,
+                    wf + 12 * b, af + 12 * b, Jf + 144 * b, ddq + 12 * b, dq_cmd + 12 * b, q_step + 12 * b);
+}
+}

@@ -1,0 +1,150 @@
+"""The product's kernel cores (csrc/mpc_core.cuh, wbc_core.cuh), compiled by g++ in warp-emulation
+mode (tests/emu), against the CPU oracle on the same seeded inputs and the same call history.
+This is the no-GPU check of the CUDA logic; the `-m gpu` tests repeat it on the real kernels."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import assert_forces_close
+
+GAITS = ("trot", "walk", "bounding", "pacing", "static")
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class EmuMPC:
+    def __init__(self, emu, B, N_gait=20):
+        self.L, self.B, self.N_gait = emu, B, N_gait
+        self.std = np.zeros((B, emu.emu_mpc_state_doubles()))
+        self.sti = np.zeros((B, emu.emu_mpc_state_ints()), np.int32)
+        self.out = np.zeros((B, 384))
+        self.info = np.zeros((B, 4), np.int32)
+        self.rho = np.zeros(B)
+        self.dbg = np.zeros((B, 1281))
+
+    def run(self, k, xref, fsteps, threads=8, max_iter=0):
+        xref, fsteps = np.ascontiguousarray(xref), np.ascontiguousarray(fsteps)
+        self.L.emu_mpc_run(self.B, C.c_double(0.02), self.N_gait, int(k == 0), max_iter, _p(xref), _p(fsteps),
+                           _p(self.std), _p(self.sti), _p(self.out), _p(self.info), _p(self.rho), _p(self.dbg), threads)
+
+    def gait(self):
+        g = np.zeros((self.B, 4 * self.N_gait))
+        for i in range(4):
+            g[:, i * self.N_gait:(i + 1) * self.N_gait] = (self.sti[:, : self.N_gait] >> i) & 1
+        return g
+
+    def sgait(self):
+        s = np.zeros((self.B, 192))
+        for k in range(16):
+            for a in range(12):
+                s[:, 12 * k + a] = (self.sti[:, 32 + k] >> (a // 3)) & 1
+        return s
+
+
+@pytest.mark.parametrize("gaits,seed", [(("trot",), 1), (GAITS, 2)])
+def test_mpc_closed_loop(emu, oracle, gaits, seed):
+    from qrw_b200 import workloads as wl
+
+    B, ticks = 24, 4
+    w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
+    e, o = EmuMPC(emu, B), oracle.OracleMPC(B)
+    x0 = None
+    for t in range(ticks):
+        xr, fs = w.inputs(t, x0)
+        e.run(t, xr, fs)
+        o.run(t, xr, fs, 8)
+        ro, io = o.get_latest_result(), o.info()
+        assert np.array_equal(e.gait(), o.get_gait())
+        assert np.array_equal(e.sgait(), o.get_Sgait())
+        assert np.array_equal(e.info[:, 0], io["iters"]), f"tick {t}"
+        assert np.array_equal(e.info[:, 1], io["status"])
+        assert np.array_equal(e.info[:, 2], io["n_factor"] - (0 if t == 0 else _prev_nf)), "KKT factorisations"
+        _prev_nf = io["n_factor"].copy()
+        np.testing.assert_allclose(e.rho, io["rho"], rtol=1e-7)
+        assert_forces_close(e.out, ro, f"x_f_applied tick {t}")
+        assert np.abs(e.out - ro).max() < 1e-7  # in practice round-off only
+        x0 = ro[:, :12].copy()
+
+
+def test_mpc_scaling_and_bounds(emu, oracle):
+    from qrw_b200 import workloads as wl
+
+    B = 6
+    w = wl.MpcWorkload(B, 3, gaits=GAITS, ticks=3)
+    e, o = EmuMPC(emu, B), oracle.OracleMPC(B)
+    x0 = None
+    for t in range(2):
+        xr, fs = w.inputs(t, x0)
+        e.run(t, xr, fs)
+        o.run(t, xr, fs, 4)
+        for b in range(B):
+            s = o.solver_state(b)
+            np.testing.assert_allclose(e.dbg[b, :384], s["D"], rtol=1e-12)
+            np.testing.assert_allclose(e.dbg[b, 384:1088], s["E"], rtol=1e-12)
+            np.testing.assert_allclose(e.dbg[b, 1088], s["c"], rtol=1e-12)
+            np.testing.assert_allclose(e.dbg[b, 1089:], o.bounds(b)[1][:192], rtol=0, atol=1e-15)
+        x0 = o.get_latest_result()[:, :12].copy()
+
+
+def test_mpc_flight_phase_and_stale_rows(emu, oracle):
+    """Quirk A.6-2: an all-swing fsteps row terminates gait processing; later steps keep the stale
+    B / S values of earlier calls."""
+    from qrw_b200 import workloads as wl
+
+    xr, fs = wl.config1_single_trot()
+    fs2 = fs.reshape(12, 20).copy()
+    fs2[:, 10:] = 0.0  # only 10 active rows on the second call
+    e, o = EmuMPC(emu, 1), oracle.OracleMPC(1)
+    for k, f in ((0, fs), (1, fs2.reshape(1, -1)), (2, fs)):
+        e.run(k, xr, f, 1)
+        o.run(k, xr, f)
+        assert np.array_equal(e.gait(), o.get_gait())
+        assert np.array_equal(e.sgait(), o.get_Sgait())
+        assert e.info[0, 0] == o.info()["iters"][0]
+        assert_forces_close(e.out, o.get_latest_result(), f"run({k})")
+
+
+def test_mpc_max_iter_returns_last_iterate(emu, oracle):
+    """Quirk A.6-8: on max_iter the last iterate is returned (status -2 / 2), never an error."""
+    from qrw_b200 import workloads as wl
+
+    xr, fs = wl.config1_single_trot()
+    e, o = EmuMPC(emu, 1), oracle.OracleMPC(1)
+    o.set_max_iter(50)
+    e.run(0, xr, fs, 1, max_iter=50)
+    o.run(0, xr, fs)
+    assert e.info[0, 0] == 50 and o.info()["iters"][0] == 50
+    assert e.info[0, 1] == o.info()["status"][0]
+    np.testing.assert_allclose(e.out, o.get_latest_result(), rtol=1e-9, atol=1e-9)
+
+
+def test_wbc_three_calls(emu, oracle):
+    from qrw_b200 import workloads as wl
+
+    B = 64
+    o = oracle.OracleWBC(B)
+    st = np.zeros((B, emu.emu_wbc_state_doubles()))
+    f_res, ddq, H, info = np.zeros((B, 12)), np.zeros((B, 6)), np.zeros((B, 144)), np.zeros((B, 4), np.int32)
+    for call in range(3):
+        M, Jc, f, R = wl.wbc_inputs(B, seed=30 + call)
+        emu.emu_wbc_run(B, int(call == 0), _p(M), _p(Jc), _p(f), _p(R), _p(st), _p(f_res), _p(ddq), _p(H), _p(info))
+        o.run(M, Jc, f, R, 4)
+        fc, dc, Hc = o.results()
+        assert np.array_equal(info[:, 0], o.info()["iters"]), f"call {call}"
+        assert_forces_close(f_res, fc, f"f_res call {call}")
+        np.testing.assert_allclose(ddq, dc, rtol=1e-5, atol=1e-4)
+        np.testing.assert_allclose(H, Hc, rtol=1e-12, atol=1e-12)
+
+
+def test_invkin(emu, oracle):
+    from qrw_b200 import workloads as wl
+
+    B = 50
+    args = wl.invkin_inputs(B, seed=4)
+    outs = [np.zeros((B, 12)) for _ in range(3)]
+    emu.emu_invkin_run(B, *[_p(a) for a in args], *[_p(o) for o in outs])
+    for a, b in zip(outs, oracle.invkin(*args)):
+        np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-12)

@@ -1,0 +1,147 @@
+"""GPU parity: the CUDA MPC path through the C ABI vs the CPU oracle on the same seeded inputs and
+the same call history (reference src/MPC.cpp:626-649 + OSQP)."""
+import numpy as np
+import pytest
+
+from conftest import assert_forces_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _closed_loop(oracle, gaits, B, seed, ticks, threads=8):
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
+    gpu, cpu = BatchedMPC(B), oracle.OracleMPC(B)
+    x0 = None
+    for t in range(ticks):
+        xr, fs = w.inputs(t, x0)
+        assert gpu.run(t, xr, fs) == 0
+        cpu.run(t, xr, fs, threads)
+        rg, rc = gpu.get_latest_result(), cpu.get_latest_result()
+        # bit-exact integer outputs (get_gait / get_Sgait, MPC.cpp:770-780)
+        assert np.array_equal(gpu.get_gait(), cpu.get_gait()), f"gait, tick {t}"
+        assert np.array_equal(gpu.get_Sgait(), cpu.get_Sgait()), f"S_gait, tick {t}"
+        ig, ic = gpu.info(), cpu.info()
+        assert np.array_equal(ig["iters"], ic["iters"]), f"ADMM iteration counts differ at tick {t}"
+        assert np.array_equal(ig["status"], ic["status"])
+        np.testing.assert_allclose(ig["rho"], ic["rho"], rtol=1e-6)
+        R = rg.reshape(B, 16, 24)
+        C = rc.reshape(B, 16, 24)
+        assert_forces_close(R[:, :, 12:], C[:, :, 12:], f"forces, tick {t}")
+        assert_forces_close(R[:, :, :12], C[:, :, :12], f"states, tick {t}")
+        x0 = rc[:, :12].copy()
+    return gpu, cpu
+
+
+def test_config1_single_trot(oracle):
+    """BASELINE config 1: scripts/test_mpc.py single trot solve; history run(0) then run(1)."""
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    xr, fs = wl.config1_single_trot()
+    gpu, cpu = BatchedMPC(1), oracle.OracleMPC(1)
+    for k in (0, 1):
+        gpu.run(k, xr, fs)
+        cpu.run(k, xr, fs)
+        assert_forces_close(gpu.get_latest_result(), cpu.get_latest_result(), f"run({k})")
+        assert np.array_equal(gpu.get_gait(), cpu.get_gait())
+    f = gpu.get_latest_result().reshape(16, 24)[:, 12:]
+    # trot: two stance feet share the weight, swing feet exactly 0 within solver accuracy
+    assert abs(f[0, 2] + f[0, 11] - 2.500002861022949 * 9.8100004196167) < 0.5
+    assert np.abs(f[0, 3:9]).max() < 1e-4
+
+
+def test_trot_batch_closed_loop(oracle):
+    _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4)
+
+
+def test_mixed_gaits_closed_loop(oracle):
+    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3)
+
+
+def test_ruiz_scaling_and_bounds_match(oracle):
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 4
+    w = wl.MpcWorkload(B, 11, gaits=("trot", "walk"), ticks=3)
+    gpu, cpu = BatchedMPC(B), oracle.OracleMPC(B)
+    gpu.enable_debug()
+    x0 = None
+    for t in range(2):
+        xr, fs = w.inputs(t, x0)
+        gpu.run(t, xr, fs)
+        cpu.run(t, xr, fs)
+        d = gpu.debug()
+        for b in range(B):
+            s = cpu.solver_state(b)
+            np.testing.assert_allclose(d["D"][b], s["D"], rtol=1e-12)
+            np.testing.assert_allclose(d["E"][b], s["E"], rtol=1e-12)
+            np.testing.assert_allclose(d["c"][b], s["c"], rtol=1e-12)
+            l, u = cpu.bounds(b)
+            np.testing.assert_allclose(d["bounds"][b], u[:192], rtol=0, atol=1e-15)
+        x0 = cpu.get_latest_result()[:, :12].copy()
+
+
+def test_state_snapshot_replays_identically():
+    """state_save / state_load: replaying a tick from the same history gives the same bits."""
+    import torch
+
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 32
+    w = wl.MpcWorkload(B, 5, gaits=("trot",), ticks=3)
+    gpu = BatchedMPC(B)
+    xr, fs = w.inputs(0)
+    gpu.run(0, xr, fs)
+    snap = torch.empty(gpu.state_bytes(), dtype=torch.uint8, device="cuda")
+    gpu.state_save(snap)
+    torch.cuda.synchronize()
+    xr1, fs1 = w.inputs(1, gpu.get_latest_result()[:, :12].copy())
+    gpu.run(1, xr1, fs1)
+    a = gpu.get_latest_result().copy()
+    gpu.state_load(snap)
+    torch.cuda.synchronize()
+    gpu.run(1, xr1, fs1)
+    assert np.array_equal(a, gpu.get_latest_result())
+
+
+def test_device_pointer_path_matches_host_path():
+    import torch
+
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 16
+    w = wl.MpcWorkload(B, 9, gaits=("trot",), ticks=2)
+    xr, fs = w.inputs(0)
+    a, b = BatchedMPC(B), BatchedMPC(B)
+    a.run(0, xr, fs)
+    b.run(0, torch.from_numpy(xr).cuda(), torch.from_numpy(fs).cuda())
+    torch.cuda.synchronize()
+    assert np.array_equal(a.get_latest_result(), b.result_tensor().cpu().numpy())
+
+
+def test_full_size_properties():
+    """BASELINE config 2 size (4096 trot instances): size-independent properties instead of the
+    oracle -- friction cone and fz bounds hold, swing-foot forces vanish, dynamics rows are met."""
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 4096
+    w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=2)
+    gpu = BatchedMPC(B)
+    xr, fs = w.inputs(0)
+    gpu.run(0, xr, fs)
+    info = gpu.info()
+    assert (info["status"] == 1).mean() > 0.99
+    ok = info["status"] == 1
+    R = gpu.get_latest_result().reshape(B, 16, 24)
+    f = R[:, :, 12:].reshape(B, 16, 4, 3)
+    mu = 0.8999999761581421
+    assert (f[ok][..., 2] > -1e-3).all() and (f[ok][..., 2] < 25 + 1e-3).all()
+    assert (np.abs(f[ok][..., 0]) <= mu * f[ok][..., 2] + 1e-3).all()
+    assert (np.abs(f[ok][..., 1]) <= mu * f[ok][..., 2] + 1e-3).all()
+    swing = w.gait(0)[:, :16] == 0
+    assert np.abs(f[ok][swing[ok]]).max() < 1e-3
+    # first dynamics row: v_z(1) = v_z(0) + dt (sum fz / m - g)
+    X0 = xr.reshape(B, 17, 12)[:, 0]
+    vz = X0[:, 8] + 0.02 * (f[:, 0, :, 2].sum(1) / 2.500002861022949 - 9.8100004196167)
+    assert np.abs(R[ok, 0, 8] - vz[ok]).max() < 1e-4
