@@ -67,6 +67,10 @@ int qrw_mpc_info_host(qrw_mpc_t* h, int* iters, int* status, double* rho, int* n
  * (D[384] | E[704] | c | unscaled dynamics bounds[192]) of every instance after the next run */
 int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter);
 int qrw_mpc_debug_host(qrw_mpc_t* h, double* out /* [B][1281] */);
+/* which CUDA kernel runs the solve: 1 (default) = one 256-thread CTA per instance (mpc_cta_core.cuh),
+ * 0 = one warp per instance (mpc_core.cuh, the round-1 v0 kernel kept for A/B checks).  Both carry the
+ * same persistent state and follow the same OSQP iterate sequence. */
+int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant);
 /* The solver state carried from call to call (scaled ADMM iterates, rho, stale B_k values, gait,
  * S_gait -- the reference keeps it inside OSQP's workspace and the MPC object).  Snapshot and
  * restore, e.g. to replay a benchmark from the same history or to checkpoint a fleet. */

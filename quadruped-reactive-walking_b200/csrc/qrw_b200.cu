@@ -17,6 +17,7 @@
 
 #include "../../include/qrw_b200.h"
 #include "mpc_core.cuh"
+#include "mpc_cta_core.cuh"
 #include "wbc_core.cuh"
 
 using namespace qrw;
@@ -56,6 +57,27 @@ __global__ void __launch_bounds__(32) mpc_solve_kernel(const MpcConst C, const i
                        st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
                        out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
     __syncwarp();
+  }
+}
+
+// CTA-per-instance MPC solve (mpc_cta_core.cuh): persistent grid of 256-thread CTAs, two per SM, pulling
+// instance indices from the global work counter.
+__global__ void __launch_bounds__(cta::NT, 2) mpc_cta_kernel(const MpcConst C, const int B, const int first,
+                                                            const double* __restrict__ xref,
+                                                            const double* __restrict__ fsteps, double* st_d,
+                                                            int* st_i, double* out, int* info, double* rho,
+                                                            double* dbg, int* counter) {
+  extern __shared__ __align__(16) double slab[];
+  int* next = reinterpret_cast<int*>(slab + cta::C_INT) + 127;
+  for (;;) {
+    if (threadIdx.x == 0) *next = atomicAdd(counter, 1);
+    __syncthreads();
+    const int b = *next;
+    if (b >= B) break;
+    cta::mpc_cta_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
+                       st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                       out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+    __syncthreads();
   }
 }
 
@@ -186,6 +208,7 @@ struct qrw_mpc {
   int B, n_steps, N_gait, device, sms;
   MpcConst C;
   bool dbg_on = false;
+  int variant = 1;  // 1 = CTA per instance (mpc_cta_kernel), 0 = warp per instance (mpc_solve_kernel)
   double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr;
@@ -284,6 +307,7 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CU(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)));
   CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
+  CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
   *out = h;
   return 0;
 }
@@ -315,11 +339,20 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
-  int grid = 3 * h->sms;  // three 75 KB slabs per SM
-  if (grid > h->B) grid = h->B;
-  mpc_solve_kernel<<<grid, 32, MPC_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
-                                                    h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
-                                                    h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+  if (h->variant == 1) {
+    int grid = 2 * h->sms;  // two 84 KB slabs (16 warps) per SM
+    if (grid > h->B) grid = h->B;
+    mpc_cta_kernel<<<grid, cta::NT, cta::CTA_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
+                                                              h->d_state, h->d_state_i, h->d_out, h->d_info,
+                                                              h->d_rho, h->dbg_on ? h->d_dbg : nullptr,
+                                                              h->d_counter);
+  } else {
+    int grid = 3 * h->sms;  // three 75 KB slabs per SM
+    if (grid > h->B) grid = h->B;
+    mpc_solve_kernel<<<grid, 32, MPC_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
+                                                      h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                      h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+  }
   ++g_launches;
   CU(cudaGetLastError());
   return 0;
@@ -397,6 +430,12 @@ int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
   if (max_iter <= 0 || max_iter % h->C.check_every != 0)
     return fail("qrw_mpc_set_max_iter: max_iter must be a positive multiple of 25 (check_termination)");
   h->C.max_iter = max_iter;
+  return 0;
+}
+int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant) {
+  if (!h) return fail("qrw_mpc_set_kernel: null handle");
+  if (variant != 0 && variant != 1) return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance) or 1 (CTA per instance)");
+  h->variant = variant;
   return 0;
 }
 int qrw_mpc_debug_host(qrw_mpc_t* h, double* out) {

@@ -55,3 +55,44 @@ QRW_HD double red_sum32(const double* red) {
 }
 
 }  // namespace qrw
+
+// ------------------------------------------------------------------------------------------
+// CTA-SPMD layer (mpc_cta_core.cuh): code written per THREAD of a multi-warp CTA, with the few
+// collective primitives below.  Under nvcc they are the hardware ones; under -DQRW_EMULATE they
+// are provided by tests/emu/cta_emu.hpp, which runs every thread of the CTA as a fiber and
+// switches at the collectives (test infrastructure only).
+// ------------------------------------------------------------------------------------------
+#if QRW_ON_GPU
+namespace qrw {
+namespace cta {
+__device__ __forceinline__ int tid() { return (int)threadIdx.x; }
+__device__ __forceinline__ void bar() { __syncthreads(); }
+__device__ __forceinline__ void wsync() { __syncwarp(); }
+__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+// max over the warp, result on every lane
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, m));
+  return v;
+}
+// out[j] = value held by lane j, j < 12, on every lane
+__device__ __forceinline__ void gather12(double v, double* out) {
+#pragma unroll
+  for (int j = 0; j < 12; ++j) out[j] = __shfl_sync(0xffffffffu, v, j);
+}
+__device__ __forceinline__ int fetch_add(int* p, int v) { return atomicAdd(p, v); }
+}  // namespace cta
+}  // namespace qrw
+#else
+namespace qrw {
+namespace cta {  // implemented in tests/emu/cta_emu.hpp
+int tid();
+void bar();
+void wsync();
+double shfl(double v, int src);
+double warp_max(double v);
+void gather12(double v, double* out);
+int fetch_add(int* p, int v);
+}  // namespace cta
+}  // namespace qrw
+#endif

@@ -128,6 +128,10 @@ class BatchedMPC:
     def set_max_iter(self, k):
         check(self._L.qrw_mpc_set_max_iter(self._h, int(k)))
 
+    def set_kernel(self, variant):
+        """1 = CTA per instance (default), 0 = warp per instance (v0)."""
+        check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
+
     def enable_debug(self):
         check(self._L.qrw_mpc_debug_host(self._h, None))
 

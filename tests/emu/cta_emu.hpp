@@ -1,0 +1,171 @@
+// tests/emu/cta_emu.hpp -- TEST INFRASTRUCTURE.  Runs the threads of one CUDA CTA as cooperative
+// fibers on the calling OS thread so that the product's per-thread kernel code (csrc/mpc_cta_core.cuh,
+// compiled with -DQRW_EMULATE) can be executed and compared with the oracle on a machine without a GPU.
+// Fibers switch only at the collectives of qrw::cta (bar, wsync, shfl, warp_max, gather12); between two
+// collectives a thread runs alone, which is a legal CUDA schedule.  x86-64 only (hand-written switch).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <vector>
+
+#if !defined(__x86_64__)
+#error "cta_emu.hpp: x86-64 only"
+#endif
+
+namespace qrw {
+namespace cta {
+
+extern "C" void qrw_emu_switch(void** save_sp, void* load_sp);
+asm(R"(
+.text
+.globl qrw_emu_switch
+.type qrw_emu_switch,@function
+qrw_emu_switch:
+  pushq %rbp
+  pushq %rbx
+  pushq %r12
+  pushq %r13
+  pushq %r14
+  pushq %r15
+  movq %rsp, (%rdi)
+  movq %rsi, %rsp
+  popq %r15
+  popq %r14
+  popq %r13
+  popq %r12
+  popq %rbx
+  popq %rbp
+  ret
+.size qrw_emu_switch,.-qrw_emu_switch
+)");
+
+struct Emu {
+  enum { RUN = 0, AT_BAR = 1, AT_WSYNC = 2, DONE = 3 };
+  int n = 0, cur = -1;
+  std::vector<void*> sp;
+  std::vector<char*> stacks;
+  std::vector<int> state;
+  std::vector<double> xch;
+  void* sched_sp = nullptr;
+  std::function<void()> body;
+  static constexpr size_t STACK = 256 * 1024;
+};
+inline thread_local Emu* g_emu = nullptr;
+
+inline void fiber_entry() {
+  Emu* e = g_emu;
+  e->body();
+  e->state[e->cur] = Emu::DONE;
+  qrw_emu_switch(&e->sp[e->cur], e->sched_sp);
+  abort();
+}
+inline void yield_as(int st) {
+  Emu* e = g_emu;
+  e->state[e->cur] = st;
+  qrw_emu_switch(&e->sp[e->cur], e->sched_sp);
+}
+
+// Run `body` once per thread of an `nthreads`-wide CTA.
+inline void run_cta(int nthreads, std::function<void()> body) {
+  Emu e;
+  e.n = nthreads;
+  e.body = std::move(body);
+  e.sp.resize(nthreads);
+  e.stacks.resize(nthreads);
+  e.state.assign(nthreads, Emu::RUN);
+  e.xch.assign(nthreads, 0.0);
+  for (int t = 0; t < nthreads; ++t) {
+    char* st = (char*)aligned_alloc(64, Emu::STACK);
+    e.stacks[t] = st;
+    uintptr_t top = ((uintptr_t)(st + Emu::STACK)) & ~(uintptr_t)15;
+    void** p = (void**)top;
+    *--p = nullptr;              // fake return address of fiber_entry
+    *--p = (void*)&fiber_entry;  // `ret` target
+    for (int r = 0; r < 6; ++r) *--p = nullptr;
+    e.sp[t] = (void*)p;
+  }
+  Emu* prev = g_emu;
+  g_emu = &e;
+  for (;;) {
+    bool progress = false;
+    int alive = 0;
+    for (int t = 0; t < nthreads; ++t) {
+      if (e.state[t] == Emu::RUN) {
+        e.cur = t;
+        qrw_emu_switch(&e.sched_sp, e.sp[t]);
+        progress = true;
+      }
+      if (e.state[t] != Emu::DONE) ++alive;
+    }
+    if (!alive) break;
+    // release barriers whose participants have all arrived
+    bool released = false;
+    bool all_bar = true;
+    for (int t = 0; t < nthreads; ++t)
+      if (e.state[t] != Emu::AT_BAR && e.state[t] != Emu::DONE) all_bar = false;
+    if (all_bar) {
+      for (int t = 0; t < nthreads; ++t)
+        if (e.state[t] == Emu::AT_BAR) e.state[t] = Emu::RUN;
+      released = true;
+    }
+    for (int w0 = 0; w0 < nthreads; w0 += 32) {
+      bool all = true, any = false;
+      for (int t = w0; t < w0 + 32 && t < nthreads; ++t) {
+        if (e.state[t] == Emu::AT_WSYNC) any = true;
+        else if (e.state[t] != Emu::DONE) all = false;
+      }
+      if (all && any) {
+        for (int t = w0; t < w0 + 32 && t < nthreads; ++t)
+          if (e.state[t] == Emu::AT_WSYNC) e.state[t] = Emu::RUN;
+        released = true;
+      }
+    }
+    if (!progress && !released) {
+      fprintf(stderr, "cta_emu: deadlock (divergent barrier)\n");
+      abort();
+    }
+  }
+  g_emu = prev;
+  for (char* s : e.stacks) free(s);
+}
+
+inline int tid() { return g_emu->cur; }
+inline void bar() { yield_as(Emu::AT_BAR); }
+inline void wsync() { yield_as(Emu::AT_WSYNC); }
+inline double shfl(double v, int src) {
+  Emu* e = g_emu;
+  const int t = e->cur;
+  e->xch[t] = v;
+  wsync();
+  const double r = e->xch[(t & ~31) + (src & 31)];
+  wsync();
+  return r;
+}
+inline double warp_max(double v) {
+  Emu* e = g_emu;
+  const int t = e->cur, w0 = t & ~31;
+  e->xch[t] = v;
+  wsync();
+  double m = e->xch[w0];
+  for (int i = 1; i < 32 && w0 + i < e->n; ++i) m = e->xch[w0 + i] > m ? e->xch[w0 + i] : m;
+  wsync();
+  return m;
+}
+inline void gather12(double v, double* out) {
+  Emu* e = g_emu;
+  const int t = e->cur, w0 = t & ~31;
+  e->xch[t] = v;
+  wsync();
+  for (int j = 0; j < 12; ++j) out[j] = e->xch[w0 + j];
+  wsync();
+}
+inline int fetch_add(int* p, int v) {
+  const int o = *p;
+  *p = o + v;
+  return o;
+}
+
+}  // namespace cta
+}  // namespace qrw

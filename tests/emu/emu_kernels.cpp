@@ -6,7 +6,8 @@
 #include <thread>
 #include <vector>
 
-#include "../../quadruped-reactive-walking_b200/csrc/mpc_core.cuh"
+#include "cta_emu.hpp"
+#include "../../quadruped-reactive-walking_b200/csrc/mpc_cta_core.cuh"
 
 using namespace qrw;
 
@@ -58,4 +59,44 @@ void emu_invkin_run(int B, const double* contacts, const double* goals, const do
     invkin_instance(contacts + 4 * b, goals + 12 * b, vgoals + 12 * b, agoals + 12 * b, posf + 12 * b, vf + 12 * b,
                     wf + 12 * b, af + 12 * b, Jf + 144 * b, ddq + 12 * b, dq_cmd + 12 * b, q_step + 12 * b);
 }
+}
+
+static std::vector<double> g_last_slab;  // debugging aid: shared slab of the last emulated CTA
+extern "C" int emu_last_slab(double* out, int cap) {
+  int n = (int)g_last_slab.size();
+  for (int i = 0; i < n && i < cap; ++i) out[i] = g_last_slab[i];
+  return n;
+}
+#ifdef QRW_DEBUG_SOLVE
+extern "C" void emu_dbgK(double* out) { memcpy(out, cta::g_dbgK, sizeof(cta::g_dbgK)); }
+#endif
+// CTA-per-instance MPC kernel core (csrc/mpc_cta_core.cuh): every thread of the 256-thread CTA is a fiber
+// (cta_emu.hpp); same contract as emu_mpc_run.
+extern "C" void emu_mpc_cta_run(int B, double dt, int N_gait, int first, int max_iter, const double* xref,
+                                const double* fsteps, double* st_d, int* st_i, double* out, int* info, double* rho,
+                                double* dbg, int nthreads) {
+  MpcConst C = make_mpc_const(dt, N_gait);
+  if (max_iter > 0) C.max_iter = max_iter;
+  auto work = [&](int t) {
+    std::vector<double> slab(cta::CTA_SLAB_DOUBLES, 0.0);
+    struct Keep {
+      std::vector<double>& s;
+      ~Keep() { g_last_slab = s; }
+    } keep{slab};
+    for (int b = t; b < B; b += nthreads) {
+      cta::run_cta(cta::NT, [&]() {
+        cta::mpc_cta_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
+                           st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                           out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+      });
+    }
+  };
+  if (nthreads <= 1) {
+    nthreads = 1;
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+    for (auto& t : th) t.join();
+  }
 }

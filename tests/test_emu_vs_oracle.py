@@ -16,8 +16,10 @@ def _p(a):
 
 
 class EmuMPC:
-    def __init__(self, emu, B, N_gait=20):
+    def __init__(self, emu, B, N_gait=20, core="cta"):
         self.L, self.B, self.N_gait = emu, B, N_gait
+        # "cta": csrc/mpc_cta_core.cuh (256-thread CTA per instance); "warp": csrc/mpc_core.cuh
+        self.fn = emu.emu_mpc_cta_run if core == "cta" else emu.emu_mpc_run
         self.std = np.zeros((B, emu.emu_mpc_state_doubles()))
         self.sti = np.zeros((B, emu.emu_mpc_state_ints()), np.int32)
         self.out = np.zeros((B, 384))
@@ -27,7 +29,7 @@ class EmuMPC:
 
     def run(self, k, xref, fsteps, threads=8, max_iter=0):
         xref, fsteps = np.ascontiguousarray(xref), np.ascontiguousarray(fsteps)
-        self.L.emu_mpc_run(self.B, C.c_double(0.02), self.N_gait, int(k == 0), max_iter, _p(xref), _p(fsteps),
+        self.fn(self.B, C.c_double(0.02), self.N_gait, int(k == 0), max_iter, _p(xref), _p(fsteps),
                            _p(self.std), _p(self.sti), _p(self.out), _p(self.info), _p(self.rho), _p(self.dbg), threads)
 
     def gait(self):
@@ -44,13 +46,14 @@ class EmuMPC:
         return s
 
 
+@pytest.mark.parametrize("core", ["cta", "warp"])
 @pytest.mark.parametrize("gaits,seed", [(("trot",), 1), (GAITS, 2)])
-def test_mpc_closed_loop(emu, oracle, gaits, seed):
+def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
     from qrw_b200 import workloads as wl
 
     B, ticks = 24, 4
     w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
-    e, o = EmuMPC(emu, B), oracle.OracleMPC(B)
+    e, o = EmuMPC(emu, B, core=core), oracle.OracleMPC(B)
     x0 = None
     for t in range(ticks):
         xr, fs = w.inputs(t, x0)
@@ -69,12 +72,13 @@ def test_mpc_closed_loop(emu, oracle, gaits, seed):
         x0 = ro[:, :12].copy()
 
 
-def test_mpc_scaling_and_bounds(emu, oracle):
+@pytest.mark.parametrize("core", ["cta", "warp"])
+def test_mpc_scaling_and_bounds(emu, oracle, core):
     from qrw_b200 import workloads as wl
 
     B = 6
     w = wl.MpcWorkload(B, 3, gaits=GAITS, ticks=3)
-    e, o = EmuMPC(emu, B), oracle.OracleMPC(B)
+    e, o = EmuMPC(emu, B, core=core), oracle.OracleMPC(B)
     x0 = None
     for t in range(2):
         xr, fs = w.inputs(t, x0)
@@ -89,7 +93,8 @@ def test_mpc_scaling_and_bounds(emu, oracle):
         x0 = o.get_latest_result()[:, :12].copy()
 
 
-def test_mpc_flight_phase_and_stale_rows(emu, oracle):
+@pytest.mark.parametrize("core", ["cta", "warp"])
+def test_mpc_flight_phase_and_stale_rows(emu, oracle, core):
     """Quirk A.6-2: an all-swing fsteps row terminates gait processing; later steps keep the stale
     B / S values of earlier calls."""
     from qrw_b200 import workloads as wl
@@ -97,7 +102,7 @@ def test_mpc_flight_phase_and_stale_rows(emu, oracle):
     xr, fs = wl.config1_single_trot()
     fs2 = fs.reshape(12, 20).copy()
     fs2[:, 10:] = 0.0  # only 10 active rows on the second call
-    e, o = EmuMPC(emu, 1), oracle.OracleMPC(1)
+    e, o = EmuMPC(emu, 1, core=core), oracle.OracleMPC(1)
     for k, f in ((0, fs), (1, fs2.reshape(1, -1)), (2, fs)):
         e.run(k, xr, f, 1)
         o.run(k, xr, f)
@@ -107,12 +112,13 @@ def test_mpc_flight_phase_and_stale_rows(emu, oracle):
         assert_forces_close(e.out, o.get_latest_result(), f"run({k})")
 
 
-def test_mpc_max_iter_returns_last_iterate(emu, oracle):
+@pytest.mark.parametrize("core", ["cta", "warp"])
+def test_mpc_max_iter_returns_last_iterate(emu, oracle, core):
     """Quirk A.6-8: on max_iter the last iterate is returned (status -2 / 2), never an error."""
     from qrw_b200 import workloads as wl
 
     xr, fs = wl.config1_single_trot()
-    e, o = EmuMPC(emu, 1), oracle.OracleMPC(1)
+    e, o = EmuMPC(emu, 1, core=core), oracle.OracleMPC(1)
     o.set_max_iter(50)
     e.run(0, xr, fs, 1, max_iter=50)
     o.run(0, xr, fs)

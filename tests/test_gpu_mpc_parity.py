@@ -8,11 +8,12 @@ from conftest import assert_forces_close
 pytestmark = pytest.mark.gpu
 
 
-def _closed_loop(oracle, gaits, B, seed, ticks, threads=8):
+def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=1):
     from qrw_b200 import BatchedMPC, workloads as wl
 
     w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
     gpu, cpu = BatchedMPC(B), oracle.OracleMPC(B)
+    gpu.set_kernel(kernel)
     x0 = None
     for t in range(ticks):
         xr, fs = w.inputs(t, x0)
@@ -51,12 +52,37 @@ def test_config1_single_trot(oracle):
     assert np.abs(f[0, 3:9]).max() < 1e-4
 
 
-def test_trot_batch_closed_loop(oracle):
-    _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4)
+@pytest.mark.parametrize("kernel", [1, 0])
+def test_trot_batch_closed_loop(oracle, kernel):
+    _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4, kernel=kernel)
 
 
-def test_mixed_gaits_closed_loop(oracle):
-    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3)
+@pytest.mark.parametrize("kernel", [1, 0])
+def test_mixed_gaits_closed_loop(oracle, kernel):
+    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3, kernel=kernel)
+
+
+def test_kernel_variants_agree_at_full_size():
+    """4096 trot instances, cold tick + one update tick: the CTA-per-instance kernel and the warp-per-instance
+    kernel follow the same iterate sequence (same iteration counts, results equal to round-off)."""
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 4096
+    w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=3)
+    a, b = BatchedMPC(B), BatchedMPC(B)
+    a.set_kernel(1)
+    b.set_kernel(0)
+    x0 = None
+    for t in range(2):
+        xr, fs = w.inputs(t, x0)
+        a.run(t, xr, fs)
+        b.run(t, xr, fs)
+        ra, rb = a.get_latest_result(), b.get_latest_result()
+        same = a.info()["iters"] == b.info()["iters"]
+        assert same.mean() > 0.995, f"tick {t}: {(~same).sum()} instances differ in iteration count"
+        assert np.abs(ra[same] - rb[same]).max() < 1e-7
+        assert np.abs(ra - rb).max() < 1e-4
+        x0 = ra[:, :12].copy()
 
 
 def test_ruiz_scaling_and_bounds_match(oracle):
