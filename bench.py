@@ -270,7 +270,7 @@ def run_b200(args):
     achieved = BYTES_PER_SOLVE * B / (kern_ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
             "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
-            "kernel": "mpc_solve_kernel", "algorithmic_bytes_per_solve": BYTES_PER_SOLVE}
+            "kernel": "mpc_v2_kernel", "algorithmic_bytes_per_solve": BYTES_PER_SOLVE}
     fp64 = None
     if hasattr(L, "qrw_fp64_peak"):
         import ctypes as C

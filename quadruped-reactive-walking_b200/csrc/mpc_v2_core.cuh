@@ -1,0 +1,1004 @@
+// mpc_v2_core.cuh -- one Solo12 centroidal-MPC solve by ONE 256-thread CTA, "force-first" KKT elimination.
+//
+// Same contract, same OSQP iterate sequence and same persistent state as mpc_core.cuh / mpc_cta_core.cuh; it
+// replaces the same reference code:
+//   MPC::run  /root/reference/src/MPC.cpp:626-649  (construct_gait :686, construct_S :665, update_ML :418,
+//   update_NK :469, call_solver :501 -> OSQP, retrieve_result :569).
+//
+// Why a third kernel.  ncu on the v1 CTA kernel (profiles/r01_ncu_mpc_v1_cta_per_instance.txt): 128 registers
+// with 534 local-memory loads per ADMM iteration, 15.2 k warp instructions per iteration, issue slots 21 % busy.
+// Its block-tridiagonal solve applies a dense 24x24 pivot inverse three times per stage and iteration.  Here
+//   * the reduced KKT matrix K = P + sigma I + A' diag(rho) A is eliminated FORCES FIRST: the 16 force
+//     blocks F_k (12x12, independent of one another) go first, the Schur complement on the states is block
+//     tridiagonal with 12x12 blocks (pivot inverses Sig_k, recurrence matrices T_k = Sig_k G_{k,k+1}).  An
+//     iteration needs 2 x 16 products with F_k^-1 (rows in REGISTERS of the row owner), 16 with Sig_k and
+//     2 x 15 with T_k (shared memory): 11 k FMA instead of 32 k, and 72 KB of shared memory so that THREE CTAs
+//     (24 warps) are resident per SM;
+//   * 16 lanes per horizon stage: lane j < 12 of stage k owns force f_k[j], state X_{k+1}[j], dynamics row
+//     (k,j) and force-enable row (k,j); lane 12+f owns the five friction-cone rows of foot f.  All iterates
+//     live in registers of their owner; stage-internal exchanges go through 16-double shared buffers and
+//     __syncwarp, only the state recurrence (one warp, 24 lanes, 15 + 15 steps) needs the two CTA barriers
+//     of an iteration.
+// It is still an exact solve of the same KKT system: the iterates differ from OSQP's by round-off only.
+#pragma once
+#include "mpc_core.cuh"
+
+namespace qrw {
+namespace v2 {
+
+constexpr int NT = 256;  // threads per CTA
+constexpr int LD = 14;   // padded row length of the 12x12 matrices in shared memory (conflict-free LDS.128)
+constexpr int MS = 12 * LD;
+
+// shared slab layout (doubles).  Everything a stage owns sits in one RECORD of SR doubles, so that a thread
+// addresses all of it (and the records of the neighbouring stages) from one base register.
+constexpr int V_SIG = 0;              // [16][12][14] Sig_k  (during factorisation: G_kk)
+constexpr int V_T = V_SIG + 16 * MS;  // [15][12][14] T_k    (during factorisation: G_{k,k+1})
+constexpr int V_REC = V_T + 15 * MS;  // [16][SR]     stage records
+constexpr int R_BA = 0, R_BB = 16, R_BC = 32, R_BD = 48;  // 4 x 16 stage-internal exchange buffers
+constexpr int R_A = 64;    // [12] sigma x_X - D_X m_k            (written by the stage's own lanes)
+constexpr int R_CC = 76;   // [12] D_X A' m_{k+1}                 (written by the lanes of stage k+1)
+constexpr int R_XT = 88;   // [12] x~_X of the stage
+constexpr int R_SP = 100;  // [12] forward-recurrence result s'_k
+constexpr int R_D = 112;   // [24] Ruiz column scaling: 0..11 force, 12..23 state
+constexpr int R_E = 136;   // [44] Ruiz row scaling: 12 dyn | 12 enable | 20 cone
+constexpr int R_BANG = 180;  // [3][12] angular block of B_k (unscaled)
+constexpr int R_B1 = 216;  // [12] scaled right-hand side of the dynamics rows
+constexpr int SR = 228;
+constexpr int V_W = V_REC + 16 * SR;  // [144] Gauss-Jordan ping-pong / T_k staging of the factorisation
+constexpr int V_SAVE = V_W + 144;     // [23][32] registers of the recurrence warp, parked while it runs the chain
+constexpr int V_RED = V_SAVE + 736;   // 128   reductions
+constexpr int V_INT = V_RED + 128;    // 128 ints
+constexpr int V2_SLAB_DOUBLES = V_INT + 64;
+constexpr int V2_SLAB_BYTES = V2_SLAB_DOUBLES * 8;
+// factorisation scratch inside a record, aliased on the iteration-only vectors [0, 112)
+constexpr int R_Y = 0;   // [12][6] F_k^-1 (D_f B0')(:, rows 6..11); dead after step (c)
+constexpr int R_N = 72;  // [36]    N_k (6x6); dead after step (d)
+static_assert(R_N + 36 <= R_D, "factorisation scratch overruns the record");
+static_assert((SR * 8) % 16 == 0 && (V_REC * 8) % 16 == 0, "records must keep 16-byte alignment");
+static_assert(V2_SLAB_BYTES <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
+
+struct Sm {
+  double *Sig, *T, *rec, *W, *save, *red;
+  int* ib;
+  QRW_HD explicit Sm(double* b)
+      : Sig(b + V_SIG), T(b + V_T), rec(b + V_REC), W(b + V_W), save(b + V_SAVE), red(b + V_RED),
+        ib(reinterpret_cast<int*>(b + V_INT)) {}
+};
+
+QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
+
+// per-thread registers.  q[] is role-dependent so that both roles fit the same 15 doubles:
+//   variable lane (j < 12): q[0..11] = row j of F_k^-1, q[12..14] = B_k(9..11, j)
+//   cone lane (j >= 12)   : q[0..4] = z, q[5..9] = y, q[10..14] = E of the foot's five cone rows
+struct Regs {
+  double q[15];
+  double xf, xX, dF, dX, z1, y1, e1, y2;
+};
+
+// unscaled dynamics row 6+r (r = 0..5) of a stage applied to a force-space vector v[0..11] held in shared memory
+QRW_HD double b0_row(const MpcConst& C, const double* Bk, const double* v, int r) {
+  if (r < 3) return C.dtm * (v[r] + v[3 + r] + v[6 + r] + v[9 + r]);
+  const double* Br = Bk + 12 * (r - 3);
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+#pragma unroll
+  for (int a = 0; a < 12; a += 3) {
+    a0 += Br[a] * v[a];
+    a1 += Br[a + 1] * v[a + 1];
+    a2 += Br[a + 2] * v[a + 2];
+  }
+  return (a0 + a1) + a2;
+}
+
+// ------------------------------------------------------------------------------------------
+// Factorisation of K, forces first.  All threads of the CTA; ends with a CTA barrier.
+//   F_k   = K(f_k, f_k)                                   -> R.q[0..11] (row j of the inverse)
+//   N_k   = e^2 (B0 D_f F_k^-1 D_f B0') e^2  (6 x 6)      -> record scratch
+//   G_kk, G_{k,k+1}: Schur complement on the states       -> Sig / T slots, then
+//   Sig_k = (G_kk - G_{k-1,k}' Sig_{k-1} G_{k-1,k})^-1,  T_k = Sig_k G_{k,k+1}
+// ------------------------------------------------------------------------------------------
+QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, double cscale, int tid) {
+  const int k = tid >> 4, j = tid & 15;
+  const bool isv = j < 12;
+  const int c3 = j % 3, ft = isv ? j / 3 : 0;
+  const int* sb = S.ib + 32;
+  double* rec = S.rec + SR * k;
+  const double* Dk = rec + R_D;
+  const double* Ek = rec + R_E;
+  const double* Bk = rec + R_BANG;
+  double* Y = rec + R_Y;
+  double* N = rec + R_N;
+  double* W = S.W;
+  double F[12];
+  const double b0 = R.q[12], b1 = R.q[13], b2 = R.q[14];
+  // ---- (a) row j of F_k
+  if (isv) {
+    const double e6 = Ek[6 + c3], e9 = Ek[9], e10 = Ek[10], e11 = Ek[11];
+    const double* Ec = Ek + 24 + 5 * ft;
+    const double c0 = Ec[0], c1 = Ec[1], c2 = Ec[2], c3e = Ec[3], c4 = Ec[4];
+    const double r4 = (25.0 * c4 < 1e-4) ? Rh.rho_eq : Rh.rho;
+    const double e2 = Ek[12 + j];
+#pragma unroll
+    for (int b = 0; b < 12; ++b) {
+      double acc = (b % 3 == c3) ? (C.dtm * e6) * (C.dtm * e6) : 0.0;
+      acc += (b0 * e9) * (Bk[b] * e9);
+      acc += (b1 * e10) * (Bk[12 + b] * e10);
+      acc += (b2 * e11) * (Bk[24 + b] * e11);
+      const double dd = R.dF * Dk[b];
+      double val = Rh.rho_eq * (acc * dd);
+      if (b / 3 == ft) {
+        const int cb = b % 3;
+        const int lo = c3 < cb ? c3 : cb, hi = c3 < cb ? cb : c3;
+        double cg = 0.0;
+        if (lo == 0 && hi == 0)
+          cg = Rh.rho * (c0 * c0 + c1 * c1);
+        else if (lo == 1 && hi == 1)
+          cg = Rh.rho * (c2 * c2 + c3e * c3e);
+        else if (lo == 2)
+          cg = Rh.rho * C.mu * C.mu * (c0 * c0 + c1 * c1 + c2 * c2 + c3e * c3e) + r4 * c4 * c4;
+        else if (lo == 0 && hi == 2)
+          cg = Rh.rho * C.mu * (c1 * c1 - c0 * c0);
+        else if (lo == 1 && hi == 2)
+          cg = Rh.rho * C.mu * (c3e * c3e - c2 * c2);
+        val += cg * dd;
+      }
+      if (b == j) {
+        val += cscale * C.wf * R.dF * R.dF + C.sigma;
+        if ((sb[k] >> ft) & 1) {
+          const double sd = e2 * R.dF;
+          val += Rh.rho_eq * sd * sd;
+        }
+      }
+      F[b] = val;
+    }
+  } else {
+#pragma unroll
+    for (int b = 0; b < 12; ++b) F[b] = (b == j) ? 1.0 : 0.0;
+  }
+  // ---- (b) Gauss-Jordan inverse inside the 16-lane group, row j in registers, pivot row by shuffle
+#pragma unroll
+  for (int p = 0; p < 12; ++p) {
+    double pr[12];
+#pragma unroll
+    for (int c = 0; c < 12; ++c) pr[c] = cta::shfl16(F[c], p);
+    const double d = 1.0 / pr[p];
+    if (j == p) {
+#pragma unroll
+      for (int c = 0; c < 12; ++c) F[c] = (c == p) ? d : pr[c] * d;
+    } else {
+      const double f = F[p];
+#pragma unroll
+      for (int c = 0; c < 12; ++c) F[c] = (c == p) ? -f * d : F[c] - f * (pr[c] * d);
+    }
+  }
+  // ---- (c) Y(j, r) = sum_b Finv(j,b) D_f(b) B0(6+r, b), r = 0..5
+  if (isv) {
+#pragma unroll
+    for (int b = 0; b < 12; ++b) R.q[b] = F[b];
+    double y[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int b = 0; b < 12; ++b) {
+      const double fd = F[b] * Dk[b];
+      y[b % 3] += C.dtm * fd;
+      y[3] += Bk[b] * fd;
+      y[4] += Bk[12 + b] * fd;
+      y[5] += Bk[24 + b] * fd;
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r) Y[6 * j + r] = y[r];
+  }
+  cta::wsync();
+  // N_k(r, r') = e_r^2 e_r'^2 sum_a B0(6+r, a) D_f(a) Y(a, r'); three entries per variable lane
+  double nv[3] = {0.0, 0.0, 0.0};
+  if (isv) {
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+      const int e = 3 * j + t, r = e / 6, rp = e - 6 * r;
+      double acc = 0.0;
+      if (r < 3) {
+        for (int f = 0; f < 4; ++f) acc += C.dtm * (Dk[3 * f + r] * Y[6 * (3 * f + r) + rp]);
+      } else {
+        const double* Br = Bk + 12 * (r - 3);
+        for (int a = 0; a < 12; ++a) acc += Br[a] * (Dk[a] * Y[6 * a + rp]);
+      }
+      const double er = Ek[6 + r], erp = Ek[6 + rp];
+      nv[t] = (er * er) * acc * (erp * erp);
+    }
+  }
+  cta::wsync();  // N overlaps the tail of Y: everybody has read Y
+  if (isv) {
+#pragma unroll
+    for (int t = 0; t < 3; ++t) N[3 * j + t] = nv[t];
+  }
+  cta::bar();
+  // ---- (d) rows of G_kk (into the Sig slot) and G_{k,k+1} (into the T slot)
+  if (isv) {
+    const int i = j;
+    const double* En = Ek + SR;  // dynamics-row scaling of stage k+1 (valid for k < 15)
+    const double* Dn = Dk + SR;  // column scaling of stage k+1
+    const double* Nn = N + SR;
+    const double r2 = Rh.rho_eq * Rh.rho_eq;
+#pragma unroll
+    for (int ip = 0; ip < 12; ++ip) {
+      double v = 0.0, o = 0.0;
+      if (ip == i) {
+        v = cscale * C.w[i] * R.dX * R.dX + C.sigma;
+        const double g = R.e1 * R.dX;
+        v += Rh.rho_eq * g * g;
+        if (k < NS - 1) {
+          const double a1 = En[i] * R.dX;
+          v += Rh.rho_eq * a1 * a1;
+          if (i >= 6) {
+            const double a2 = C.dt * En[i - 6] * R.dX;
+            v += Rh.rho_eq * a2 * a2;
+          }
+          o = -Rh.rho_eq * (En[i] * En[i]) * (R.dX * Dn[12 + i]);
+        }
+      }
+      if (k < NS - 1) {
+        const int lo = i < ip ? i : ip, hi = i < ip ? ip : i;
+        if (hi - lo == 6) v += Rh.rho_eq * C.dt * En[lo] * En[lo] * Dk[12 + lo] * Dk[12 + hi];
+        if (ip == i - 6) o = -Rh.rho_eq * C.dt * (En[ip] * En[ip]) * (R.dX * Dn[12 + ip]);
+      }
+      if (i >= 6 && ip >= 6) {
+        const int e = 6 * (i - 6) + (ip - 6);
+        double nn = N[e];
+        if (k < NS - 1) {
+          const double nx = Nn[e];
+          nn += nx;
+          o += r2 * (R.dX * Dn[12 + ip]) * nx;
+        }
+        v -= r2 * (R.dX * Dk[12 + ip]) * nn;
+      }
+      S.Sig[MS * k + LD * i + ip] = v;
+      if (k < NS - 1) S.T[MS * k + LD * i + ip] = o;
+    }
+  }
+  cta::bar();
+  // ---- (e) block-tridiagonal LDL' of the state system, one stage after the other (144 threads, entry per thread)
+  const int ei = tid / 12, ej = tid - 12 * ei;  // entry (ei, ej) for tid < 144
+  const bool ent = tid < 144;
+  for (int s = 0; s < NS; ++s) {
+    double* G = S.Sig + MS * s;
+    // Gauss-Jordan inverse, ping-pong G <-> W (12 pivots: the result is back in G)
+    for (int p = 0; p < 12; ++p) {
+      const double* Wc = (p & 1) ? W : G;
+      double* Wn = (p & 1) ? G : W;
+      const int ldc = (p & 1) ? 12 : LD, ldn = (p & 1) ? LD : 12;
+      if (ent) {
+        const double d = 1.0 / Wc[ldc * p + p];
+        double v;
+        if (ei == p)
+          v = (ej == p) ? d : Wc[ldc * p + ej] * d;
+        else if (ej == p)
+          v = -Wc[ldc * ei + p] * d;
+        else
+          v = Wc[ldc * ei + ej] - Wc[ldc * ei + p] * (Wc[ldc * p + ej] * d);
+        Wn[ldn * ei + ej] = v;
+      }
+      cta::bar();
+    }
+    if (s == NS - 1) break;
+    double* O = S.T + MS * s;
+    // T_s = Sig_s G_{s,s+1}  (staged in W)
+    if (ent) {
+      double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m < 12; ++m) acc += G[LD * ei + m] * O[LD * m + ej];
+      W[12 * ei + ej] = acc;
+    }
+    cta::bar();
+    // G_{s+1,s+1} -= G_{s,s+1}' T_s ;  then the T slot takes T_s
+    double tv = 0.0;
+    if (ent) {
+      double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m < 12; ++m) acc += O[LD * m + ei] * W[12 * m + ej];
+      S.Sig[MS * (s + 1) + LD * ei + ej] -= acc;
+      tv = W[12 * ei + ej];
+    }
+    cta::bar();
+    if (ent) O[LD * ei + ej] = tv;
+  }
+  // the scratch overlapped CC of the last stage, which nobody writes and the recurrence reads as zero
+  if (tid < 12) S.rec[SR * (NS - 1) + R_CC + tid] = 0.0;
+  cta::bar();
+}
+
+// ------------------------------------------------------------------------------------------
+// State recurrences of one KKT solve, ONE warp, fully unrolled, 12-term dot products per lane:
+//   s_k   = A_k + CC_k                                             right-hand side of the state system
+//   s'_0  = s_0 ,  s'_{k+1} = s_{k+1} - T_k' s'_k                  forward   (lane i < 12; upper half mirrors)
+//   X_15  = Sig_15 s'_15 ,  X_k = Sig_k s'_k - T_k X_{k+1}         backward: lanes 16.. compute Sig_{k-1} s'_{k-1}
+//                                                                  one step ahead of the chain run by lanes 0..11
+// The vector of a step is broadcast through the record (STS, __syncwarp, LDS.128), not by shuffles.
+// ------------------------------------------------------------------------------------------
+QRW_HD void state_recurrence(const Sm& S, int lane) {
+  const int i0 = lane & 15;
+  const bool up = lane >= 16;
+  const int i = i0 < 12 ? i0 : 11;
+  const bool wr = lane < 12;
+  double* rec = S.rec;
+  double p = rec[R_A + i] + rec[R_CC + i];
+  if (wr) rec[R_SP + i] = p;
+#pragma unroll
+  for (int k = 0; k < NS - 1; ++k) {
+    const double* T = S.T + MS * k + i;
+    double* rn = rec + SR * (k + 1);
+    double tc[12];
+#pragma unroll
+    for (int jj = 0; jj < 12; ++jj) tc[jj] = T[LD * jj];
+    double a0 = rn[R_A + i] + rn[R_CC + i], a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    cta::wsync();
+    const double* pp = rec + SR * k + R_SP;
+    double pv[12];
+    cta::lds12(pp, pv);
+    cta::sched_fence();
+#pragma unroll
+    for (int jj = 8; jj >= 0; jj -= 4) {  // last-loaded elements first: every load is in flight before the first FMA
+      a0 -= tc[jj] * pv[jj];
+      a1 -= tc[jj + 1] * pv[jj + 1];
+      a2 -= tc[jj + 2] * pv[jj + 2];
+      a3 -= tc[jj + 3] * pv[jj + 3];
+    }
+    p = (a0 + a1) + (a2 + a3);
+    if (wr) rn[R_SP + i] = p;
+  }
+  cta::wsync();
+  // v_15 on every lane
+  double vcur;
+  {
+    const double* Sg = S.Sig + MS * (NS - 1) + LD * i;
+    const double* sp = rec + SR * (NS - 1) + R_SP;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+    for (int jj = 0; jj < 12; jj += 4) {
+      a0 += Sg[jj] * sp[jj];
+      a1 += Sg[jj + 1] * sp[jj + 1];
+      a2 += Sg[jj + 2] * sp[jj + 2];
+      a3 += Sg[jj + 3] * sp[jj + 3];
+    }
+    vcur = (a0 + a1) + (a2 + a3);
+  }
+#pragma unroll
+  for (int k = NS - 1; k >= 0; --k) {
+    // lower half: T_k X_{k+1} (nothing for k = 15); upper half: Sig_{k-1} s'_{k-1} (nothing for k = 0)
+    const int kt = (k < NS - 1) ? k : 0, ks = (k > 0) ? k - 1 : 0;
+    const double* mp = up ? (S.Sig + MS * ks + LD * i) : (S.T + MS * kt + LD * i);
+    const double* vp = up ? (rec + SR * ks + R_SP) : (rec + SR * (kt + 1) + R_XT);
+    double mr[12];
+#pragma unroll
+    for (int jj = 0; jj < 12; ++jj) mr[jj] = mp[jj];
+    if (k < NS - 1) cta::wsync();
+    double vv[12];
+    cta::lds12(vp, vv);
+    cta::sched_fence();
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+    for (int jj = 8; jj >= 0; jj -= 4) {
+      a0 += mr[jj] * vv[jj];
+      a1 += mr[jj + 1] * vv[jj + 1];
+      a2 += mr[jj + 2] * vv[jj + 2];
+      a3 += mr[jj + 3] * vv[jj + 3];
+    }
+    const double d = (a0 + a1) + (a2 + a3);
+    const double X = (k < NS - 1) ? vcur - d : vcur;
+    if (wr) rec[SR * k + R_XT + i] = X;
+    if (k > 0) vcur = cta::shfl_xor(d, 16);  // lanes 0..11 pick up v_{k-1} from lanes 16..27
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// One full MPC::run for one instance; every thread of the CTA calls it with the same arguments.
+// Same I/O contract as mpc_solve_instance (mpc_core.cuh).  recw = the warp that runs the recurrences.
+// ------------------------------------------------------------------------------------------
+QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, const double* fs, double* st_d,
+                         int* st_i, int first, double* out, int* info, double* rho_out, double* dbg, int recw) {
+  const Sm S(slab);
+  const int tid = cta::tid();
+  const int k = tid >> 4, j = tid & 15, w = tid >> 5, l = tid & 31;
+  const int NG = C.N_gait;
+  int* gait = S.ib;       // [32]
+  int* sb = S.ib + 32;    // [16] S_gait bits per step (bit f set = foot f swings, force pinned to 0)
+  int* itmp = S.ib + 48;  // [64]
+  Regs R;
+  const bool isv = j < 12;
+  const int c3 = j % 3, ft = isv ? j / 3 : 0;
+  const int cf = isv ? 0 : j - 12;  // foot of a cone lane
+  double* rec = S.rec + SR * k;
+  double* BAk = rec + R_BA;
+  double* BBk = rec + R_BB;
+  double* BCk = rec + R_BC;
+  double* BDk = rec + R_BD;
+  double* Bk = rec + R_BANG;
+  double* Dk = rec + R_D;
+  double* Ek = rec + R_E;
+
+  // ---- load the state carried between calls
+  for (int i = tid; i < 576; i += NT) S.rec[SR * (i / 36) + R_BANG + (i % 36)] = first ? 0.0 : st_d[ST_BANG + i];
+  if (tid < 32) gait[tid] = first ? 0 : st_i[tid];
+  if (tid < NS) sb[tid] = first ? 0 : st_i[32 + tid];
+#pragma unroll
+  for (int t = 0; t < 15; ++t) R.q[t] = 0.0;
+  R.xf = R.xX = R.z1 = R.y1 = R.y2 = 0.0;
+  if (!first) {
+    if (isv) {
+      R.xf = st_d[ST_X + gvar(k, j)];
+      R.xX = st_d[ST_X + gvar(k, 12 + j)];
+      R.z1 = st_d[ST_Z + grow(k, j)];
+      R.y1 = st_d[ST_Y + grow(k, j)];
+      R.y2 = st_d[ST_Y + grow(k, 12 + j)];
+    } else {
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        R.q[q] = st_d[ST_Z + grow(k, 24 + 5 * cf + q)];
+        R.q[5 + q] = st_d[ST_Y + grow(k, 24 + 5 * cf + q)];
+      }
+    }
+  }
+  double rho_now = first ? C.rho0 : st_d[ST_RHO];
+
+  // ---- construct_gait (MPC.cpp:686-701), construct_S (:665-681): warp 0
+  if (w == 0) {
+    int zero = 1, bits = 0;
+    if (l < NG) {
+      for (int c = 0; c < 12; ++c) {
+        const double v = fs[l + NG * c];
+        if (!(fabs(v) <= 1e-12)) zero = 0;
+      }
+      for (int f = 0; f < 4; ++f)
+        if (fs[l + NG * (3 * f)] != 0.0) bits |= (1 << f);
+    }
+    itmp[l] = zero;
+    itmp[32 + l] = bits;
+  }
+  cta::bar();
+  int nact = 0;
+  while (nact < NG && !itmp[nact]) ++nact;
+  const int overrun = (nact >= NG);
+  cta::bar();
+  if (w == 0) {
+    if (l < nact)
+      gait[l] = itmp[32 + l];
+    else if (l == nact && l < NG)
+      gait[l] = 0;
+  }
+  cta::bar();
+  int nS = 0;
+  while (nS < NG && gait[nS] != 0) ++nS;
+  cta::bar();
+  if (tid < nS && tid < NS) sb[tid] = (~gait[tid]) & 15;
+  // ---- B_k angular blocks (create_ML :213-232 on the first call, update_ML :418-452 after)
+  if (tid < NS && (first || tid < nS)) {
+    const int kk = tid;
+    const double yaw = xref[5 + 12 * kk];
+    const double cy = cos(yaw), sy = sin(yaw);
+    const double Rm[3][3] = {{cy, -sy, 0.0}, {sy, cy, 0.0}, {0.0, 0.0, 1.0}};
+    double T[3][3], M[3][3], Ii[3][3];
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) {
+        double acc = 0.0;
+        for (int q = 0; q < 3; ++q) acc += Rm[q][a] * C.gI[3 * q + b];
+        T[a][b] = acc;
+      }
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) {
+        double acc = 0.0;
+        for (int q = 0; q < 3; ++q) acc += T[a][q] * Rm[q][b];
+        M[a][b] = acc;
+      }
+    const double c00 = M[1][1] * M[2][2] - M[1][2] * M[2][1];
+    const double c10 = M[1][2] * M[2][0] - M[1][0] * M[2][2];
+    const double c20 = M[1][0] * M[2][1] - M[1][1] * M[2][0];
+    const double det = c00 * M[0][0] + c10 * M[0][1] + c20 * M[0][2];
+    const double id = 1.0 / det;
+    Ii[0][0] = c00 * id;
+    Ii[1][0] = c10 * id;
+    Ii[2][0] = c20 * id;
+    Ii[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id;
+    Ii[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id;
+    Ii[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
+    Ii[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id;
+    Ii[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
+    Ii[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+    for (int f = 0; f < 4; ++f) {
+      double v[3];
+      for (int r = 0; r < 3; ++r)
+        v[r] = first ? (C.foot[4 * r + f] - xref[r + 12 * kk])
+                     : (fs[kk + NG * (3 * f + r)] - (xref[r + 12 * kk] + C.off_com[r]));
+      const double Sk[3][3] = {{0.0, -v[2], v[1]}, {v[2], 0.0, -v[0]}, {-v[1], v[0], 0.0}};
+      for (int r = 0; r < 3; ++r)
+        for (int c2 = 0; c2 < 3; ++c2) {
+          double acc = 0.0;
+          for (int q = 0; q < 3; ++q) acc += Ii[r][q] * Sk[q][c2];
+          S.rec[SR * kk + R_BANG + 12 * r + 3 * f + c2] = C.dt * acc;
+        }
+    }
+  }
+  // ---- right-hand side of the dynamics rows (create_NK :261-289 / update_NK :469-486), row owners
+  double bnd = 0.0;
+  if (isv) {
+    const int i = j;
+    double base = (i == 8) ? -C.g8 : 0.0;
+    double sm = 0.0;
+    if (k == 0) {
+      double acc = 0.0;
+      acc += 1.0 * (-xref[i]);
+      if (i < 6) acc += C.dt * (-xref[i + 6]);
+      base += acc;
+    } else {
+      sm += -1.0 * xref[i + 12 * k];
+      if (i < 6) sm += -C.dt * xref[i + 6 + 12 * k];
+    }
+    sm += 1.0 * xref[i + 12 * (k + 1)];
+    bnd = base + sm;
+    if (dbg) dbg[NX + NR + 1 + 12 * k + i] = bnd;
+  }
+  // Ruiz start values
+  double e2 = 1.0;
+  R.dF = R.dX = R.e1 = 1.0;
+  if (isv) {
+    Dk[j] = 1.0;
+    Dk[12 + j] = 1.0;
+    Ek[j] = 1.0;
+    Ek[12 + j] = 1.0;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+      R.q[10 + q] = 1.0;
+      Ek[24 + 5 * cf + q] = 1.0;
+    }
+  }
+  cta::bar();
+  if (isv) {
+    R.q[12] = Bk[j];
+    R.q[13] = Bk[12 + j];
+    R.q[14] = Bk[24 + j];
+  }
+  const int bit = isv ? ((sb[k] >> ft) & 1) : 0;
+
+  // ---- Ruiz equilibration, 10 passes (OSQP scale_data; rerun on every call, MPC.cpp:541,548)
+  double cscale = 1.0;
+  for (int pass = 0; pass < 10; ++pass) {
+    double dDF = 1.0, dDX = 1.0, dE1 = 1.0, dE2 = 1.0, dEc[5];
+    if (isv) {
+      const int i = j;
+      // column of f_k[j]
+      const double d = R.dF;
+      double nrm = cscale * C.wf * d * d;
+      nrm = dmax(nrm, C.dtm * Ek[6 + c3] * d);
+      nrm = dmax(nrm, fabs(R.q[12]) * Ek[9] * d);
+      nrm = dmax(nrm, fabs(R.q[13]) * Ek[10] * d);
+      nrm = dmax(nrm, fabs(R.q[14]) * Ek[11] * d);
+      if (bit) nrm = dmax(nrm, e2 * d);
+      const double* Ec = Ek + 24 + 5 * ft;
+      if (c3 == 0) {
+        nrm = dmax(nrm, dmax(Ec[0], Ec[1]) * d);
+      } else if (c3 == 1) {
+        nrm = dmax(nrm, dmax(Ec[2], Ec[3]) * d);
+      } else {
+        const double em = dmax(dmax(Ec[0], Ec[1]), dmax(Ec[2], Ec[3]));
+        nrm = dmax(nrm, C.mu * em * d);
+        nrm = dmax(nrm, Ec[4] * d);
+      }
+      dDF = 1.0 / sqrt(limit_scaling(nrm));
+      // column of X_{k+1}[i]
+      const double dx = R.dX;
+      double nx = fabs(cscale * C.w[i] * dx * dx);
+      nx = dmax(nx, R.e1 * dx);
+      if (k < NS - 1) {
+        nx = dmax(nx, Ek[SR + i] * dx);
+        if (i >= 6) nx = dmax(nx, C.dt * Ek[SR + i - 6] * dx);
+      }
+      dDX = 1.0 / sqrt(limit_scaling(nx));
+      // dynamics row (k, i)
+      const double e = R.e1;
+      double nr = e * dx;
+      if (k > 0) {
+        nr = dmax(nr, e * Dk[-SR + 12 + i]);
+        if (i < 6) nr = dmax(nr, C.dt * e * Dk[-SR + 18 + i]);
+      }
+      if (i >= 6) {
+        if (i < 9) {
+          for (int f = 0; f < 4; ++f) nr = dmax(nr, C.dtm * e * Dk[3 * f + i - 6]);
+        } else {
+          const double* Br = Bk + 12 * (i - 9);
+          for (int b = 0; b < 12; ++b) nr = dmax(nr, fabs(Br[b]) * e * Dk[b]);
+        }
+      }
+      dE1 = 1.0 / sqrt(limit_scaling(nr));
+      const double nf = bit ? e2 * d : 0.0;
+      dE2 = 1.0 / sqrt(limit_scaling(nf));
+    } else {
+      const double* Df = Dk + 3 * cf;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        const double e = R.q[10 + q];
+        const double nr = (q == 4) ? e * Df[2] : dmax(e * Df[q >> 1], C.mu * e * Df[2]);
+        dEc[q] = 1.0 / sqrt(limit_scaling(nr));
+      }
+    }
+    cta::bar();
+    double psum = 0.0;
+    if (isv) {
+      R.dF *= dDF;
+      R.dX *= dDX;
+      R.e1 *= dE1;
+      e2 *= dE2;
+      Dk[j] = R.dF;
+      Dk[12 + j] = R.dX;
+      Ek[j] = R.e1;
+      Ek[12 + j] = e2;
+      psum = fabs(cscale * C.wf * R.dF * R.dF) + fabs(cscale * C.w[j] * R.dX * R.dX);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        R.q[10 + q] *= dEc[q];
+        Ek[24 + 5 * cf + q] = R.q[10 + q];
+      }
+    }
+    // cost normalisation: mean of the column norms of the scaled P (diagonal)
+#pragma unroll
+    for (int m = 8; m > 0; m >>= 1) psum += cta::shfl_xor(psum, m);
+    if (j == 0) S.red[k] = psum;
+    cta::bar();
+    double tot = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < NS; ++kk) tot += S.red[kk];
+    double c_temp = tot / (double)NX;
+    c_temp = dmax(c_temp, 1.0);  // ||q||_inf = 0 -> limit_scaling -> 1
+    c_temp = limit_scaling(c_temp);
+    cscale *= 1.0 / c_temp;
+  }
+  cta::bar();
+  const double cinv = 1.0 / cscale;
+  if (dbg) {
+    if (isv) {
+      dbg[gvar(k, j)] = R.dF;
+      dbg[gvar(k, 12 + j)] = R.dX;
+      dbg[NX + grow(k, j)] = R.e1;
+      dbg[NX + grow(k, 12 + j)] = e2;
+    } else {
+#pragma unroll
+      for (int q = 0; q < 5; ++q) dbg[NX + grow(k, 24 + 5 * cf + q)] = R.q[10 + q];
+    }
+    if (tid == 0) dbg[NX + NR] = cscale;
+  }
+  if (isv) rec[R_B1 + j] = R.e1 * bnd;
+
+  // ---- KKT factorisation
+  RhoSet Rh(rho_now);
+  int n_factor = 0;
+  bool refactor = true;
+
+  // ---- ADMM (osqp_solve)
+  int status = ST_UNSOLVED;
+  int iter = 0;
+  for (iter = 1; iter <= C.max_iter; ++iter) {
+    if (refactor) {  // first iteration and after every rho update (single inlined call site)
+      factor(C, S, R, Rh, cscale, tid);
+      ++n_factor;
+      refactor = false;
+    }
+    // (1) row values u = E (rho z - y); cone lanes hand the foot's A' contribution to the force owners
+    double u1 = 0.0, u2 = 0.0;
+    if (isv) {
+      u1 = R.e1 * (Rh.rho_eq * R.z1 - R.y1);
+      if (bit) u2 = Ek[12 + j] * (Rh.rho_eq * 0.0 - R.y2);
+      BAk[j] = u1;
+    } else {
+      double uc[5];
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        const bool eq = (q == 4) && (25.0 * R.q[14] < 1e-4);
+        uc[q] = R.q[10 + q] * ((eq ? Rh.rho_eq : Rh.rho) * R.q[q] - R.q[5 + q]);
+      }
+      BDk[3 * cf] = uc[0] - uc[1];
+      BDk[3 * cf + 1] = uc[2] - uc[3];
+      BDk[3 * cf + 2] = -C.mu * (uc[0] + uc[1] + uc[2] + uc[3]) - uc[4];
+    }
+    cta::wsync();
+    // (2) t_f = sigma x_f + D_f (A' u)_f
+    double tf = 0.0;
+    if (isv) {
+      double v = C.dtm * BAk[6 + c3];
+      v += R.q[12] * BAk[9];
+      v += R.q[13] * BAk[10];
+      v += R.q[14] * BAk[11];
+      if (bit) v += u2;
+      v += BDk[j];
+      tf = C.sigma * R.xf + R.dF * v;
+      BBk[j] = tf;
+    }
+    cta::wsync();
+    // (3) u_f = F^-1 t_f
+    double uf = 0.0;
+    if (isv) {
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+      for (int b = 0; b < 12; b += 4) {
+        a0 += R.q[b] * BBk[b];
+        a1 += R.q[b + 1] * BBk[b + 1];
+        a2 += R.q[b + 2] * BBk[b + 2];
+        a3 += R.q[b + 3] * BBk[b + 3];
+      }
+      uf = (a0 + a1) + (a2 + a3);
+      BAk[j] = R.dF * uf;
+    }
+    cta::wsync();
+    // (4) m = u - rho E (B0 D_f u_f): what the state system sees of the dynamics rows;
+    //     A_k = sigma x_X - D_X m_k (own record), CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
+    double mk = 0.0;
+    if (isv) {
+      double wv = 0.0;
+      if (j >= 6) wv = R.e1 * b0_row(C, Bk, BAk, j - 6);
+      mk = u1 - Rh.rho_eq * (R.e1 * wv);
+      BBk[j] = mk;
+      rec[R_A + j] = C.sigma * R.xX - R.dX * mk;
+    }
+    cta::wsync();
+    if (isv && k > 0) {
+      double v = mk;
+      if (j >= 6) v += C.dt * BBk[j - 6];
+      rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
+    }
+    cta::bar();
+    if (w == recw) {
+      // park this warp's solver state in shared memory: the chain then has the registers to keep every load
+      // of a step in flight at once (with the state live ptxas serialised LDS -> DFMA -> LDS, r01 ncu)
+      double* sv = S.save + l;
+#pragma unroll
+      for (int t = 0; t < 15; ++t) sv[32 * t] = R.q[t];
+      sv[32 * 15] = R.xf;
+      sv[32 * 16] = R.xX;
+      sv[32 * 17] = R.z1;
+      sv[32 * 18] = R.y1;
+      sv[32 * 19] = R.y2;
+      sv[32 * 20] = uf;
+      state_recurrence(S, l);
+#pragma unroll
+      for (int t = 0; t < 15; ++t) R.q[t] = sv[32 * t];
+      R.xf = sv[32 * 15];
+      R.xX = sv[32 * 16];
+      R.z1 = sv[32 * 17];
+      R.y1 = sv[32 * 18];
+      R.y2 = sv[32 * 19];
+      uf = sv[32 * 20];
+      if (isv) {
+        R.dF = Dk[j];
+        R.dX = Dk[12 + j];
+        R.e1 = Ek[j];
+      }
+    }
+    cta::bar();
+    // (5) dynamics rows applied to the new states; h = rho D_f B0' E^2 (...)
+    double xtX = 0.0, smX = 0.0;
+    if (isv) {
+      xtX = rec[R_XT + j];
+      smX = -(R.dX * xtX);
+      if (k > 0) {
+        smX += Dk[-SR + 12 + j] * rec[-SR + R_XT + j];
+        if (j < 6) smX += C.dt * (Dk[-SR + 18 + j] * rec[-SR + R_XT + j + 6]);
+      }
+      BAk[j] = R.e1 * (R.e1 * smX);
+    }
+    cta::wsync();
+    if (isv) {
+      double v = C.dtm * BAk[6 + c3];
+      v += R.q[12] * BAk[9];
+      v += R.q[13] * BAk[10];
+      v += R.q[14] * BAk[11];
+      BBk[j] = Rh.rho_eq * (R.dF * v);
+    }
+    cta::wsync();
+    // (6) x~_f = u_f - F^-1 h
+    double xtf = 0.0;
+    if (isv) {
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+      for (int b = 0; b < 12; b += 4) {
+        a0 += R.q[b] * BBk[b];
+        a1 += R.q[b + 1] * BBk[b + 1];
+        a2 += R.q[b + 2] * BBk[b + 2];
+        a3 += R.q[b + 3] * BBk[b + 3];
+      }
+      xtf = uf - ((a0 + a1) + (a2 + a3));
+      BCk[j] = R.dF * xtf;
+    }
+    cta::wsync();
+    // (7) z~ = A x~, relaxation, projection, dual update, x update
+    if (isv) {
+      double sm = smX;
+      if (j >= 6) sm += b0_row(C, Bk, BCk, j - 6);
+      const double zt = R.e1 * sm;
+      const double zr = C.alpha * zt + (1.0 - C.alpha) * R.z1;
+      const double zn = rec[R_B1 + j];
+      R.y1 += Rh.rho_eq * (zr - zn);
+      R.z1 = zn;
+      // force-enable row (k, j): l = u = 0
+      const double zt2 = bit ? Ek[12 + j] * BCk[j] : 0.0;
+      const double zr2 = C.alpha * zt2 + (1.0 - C.alpha) * 0.0;
+      R.y2 += Rh.rho_eq * (zr2 - 0.0);
+      R.xf = C.alpha * xtf + (1.0 - C.alpha) * R.xf;
+      R.xX = C.alpha * xtX + (1.0 - C.alpha) * R.xX;
+    } else {
+      const double fx = BCk[3 * cf], fy = BCk[3 * cf + 1], fz = BCk[3 * cf + 2];
+      const bool eq4 = 25.0 * R.q[14] < 1e-4;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        double row;
+        if (q == 4)
+          row = -fz;
+        else {
+          const double t = (q >> 1) ? fy : fx;
+          row = ((q & 1) ? -t : t) - C.mu * fz;
+        }
+        const bool eq = (q == 4) && eq4;
+        const double rr = eq ? Rh.rho_eq : Rh.rho, ri = eq ? Rh.rinv_eq : Rh.rinv;
+        const double e = R.q[10 + q];
+        const double zt = e * row;
+        const double zr = C.alpha * zt + (1.0 - C.alpha) * R.q[q];
+        double zn = zr + ri * R.q[5 + q];
+        if (q == 4) zn = dmax(zn, -25.0 * e);
+        zn = dmin(zn, 0.0);
+        R.q[5 + q] += rr * (zr - zn);
+        R.q[q] = zn;
+      }
+    }
+    if (iter % C.check_every == 0) {
+      // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
+      cta::bar();  // everyone is done with the exchange buffers of this iteration
+      if (isv) {
+        BCk[j] = R.dF * R.xf;
+        rec[R_XT + j] = R.dX * R.xX;
+        rec[R_A + j] = R.e1 * R.y1;
+        BBk[j] = Ek[12 + j] * R.y2;
+      } else {
+        double uc[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) uc[q] = R.q[10 + q] * R.q[5 + q];
+        BDk[3 * cf] = uc[0] - uc[1];
+        BDk[3 * cf + 1] = uc[2] - uc[3];
+        BDk[3 * cf + 2] = -C.mu * (uc[0] + uc[1] + uc[2] + uc[3]) - uc[4];
+      }
+      cta::bar();
+      double m[12];
+#pragma unroll
+      for (int q = 0; q < 12; ++q) m[q] = 0.0;
+      auto row_acc = [&](double ax, double zi, double e) {
+        const double einv = 1.0 / e, rs = ax - zi;
+        m[0] = dmax(m[0], fabs(rs));
+        m[1] = dmax(m[1], fabs(einv * rs));
+        m[2] = dmax(m[2], fabs(zi));
+        m[3] = dmax(m[3], fabs(einv * zi));
+        m[4] = dmax(m[4], fabs(ax));
+        m[5] = dmax(m[5], fabs(einv * ax));
+      };
+      auto var_acc = [&](double aty, double px, double d) {
+        const double ds = px + aty, dinv = 1.0 / d;
+        m[6] = dmax(m[6], fabs(ds));
+        m[7] = dmax(m[7], fabs(dinv * ds));
+        m[8] = dmax(m[8], fabs(aty));
+        m[9] = dmax(m[9], fabs(dinv * aty));
+        m[10] = dmax(m[10], fabs(px));
+        m[11] = dmax(m[11], fabs(dinv * px));
+      };
+      if (isv) {
+        double sm = -rec[R_XT + j];
+        if (k > 0) {
+          sm += rec[-SR + R_XT + j];
+          if (j < 6) sm += C.dt * rec[-SR + R_XT + j + 6];
+        }
+        if (j >= 6) sm += b0_row(C, Bk, BCk, j - 6);
+        row_acc(R.e1 * sm, R.z1, R.e1);
+        row_acc(bit ? Ek[12 + j] * BCk[j] : 0.0, 0.0, Ek[12 + j]);
+        // force variable
+        const double* u = rec + R_A;
+        double v = C.dtm * u[6 + c3];
+        v += R.q[12] * u[9];
+        v += R.q[13] * u[10];
+        v += R.q[14] * u[11];
+        if (bit) v += BBk[j];
+        v += BDk[j];
+        var_acc(R.dF * v, (cscale * C.wf * R.dF * R.dF) * R.xf, R.dF);
+        // state variable
+        double vx = -u[j];
+        if (k < NS - 1) {
+          vx += u[SR + j];
+          if (j >= 6) vx += C.dt * u[SR + j - 6];
+        }
+        var_acc(R.dX * vx, (cscale * C.w[j] * R.dX * R.dX) * R.xX, R.dX);
+      } else {
+        const double fx = BCk[3 * cf], fy = BCk[3 * cf + 1], fz = BCk[3 * cf + 2];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          double row;
+          if (q == 4)
+            row = -fz;
+          else {
+            const double t = (q >> 1) ? fy : fx;
+            row = ((q & 1) ? -t : t) - C.mu * fz;
+          }
+          row_acc(R.q[10 + q] * row, R.q[q], R.q[10 + q]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 12; ++q) {
+        m[q] = cta::warp_max(m[q]);
+        if (l == 0) S.red[16 + 12 * w + q] = m[q];
+      }
+      cta::bar();
+#pragma unroll
+      for (int q = 0; q < 12; ++q) {
+        double v = S.red[16 + q];
+        for (int ww = 1; ww < NT / 32; ++ww) v = dmax(v, S.red[16 + 12 * ww + q]);
+        m[q] = v;
+      }
+      const double pri_s = m[0], pri_u = m[1], nz_s = m[2], nz_u = m[3], nax_s = m[4], nax_u = m[5], dua_s = m[6],
+                   dua_u = cinv * m[7], naty_s = m[8], naty_u = m[9], npx_s = m[10], npx_u = m[11];
+      if (pri_u > 1e30 || dua_u > 1e30) {
+        status = ST_NON_CVX;
+        break;
+      }
+      const double eps_pri = C.eps_abs + C.eps_rel * dmax(nz_u, nax_u);
+      const double eps_dua = C.eps_abs + C.eps_rel * (cinv * dmax(naty_u, npx_u));
+      if (pri_u < eps_pri && dua_u < eps_dua) {
+        status = ST_SOLVED;
+        break;
+      }
+      if (iter == C.max_iter) {
+        const double t1 = 10.0 * C.eps_abs + 10.0 * C.eps_rel * dmax(nz_u, nax_u);
+        const double t2 = 10.0 * C.eps_abs + 10.0 * C.eps_rel * (cinv * dmax(naty_u, npx_u));
+        status = (pri_u < t1 && dua_u < t2) ? ST_SOLVED_INACCURATE : ST_MAX_ITER;
+      }
+      if (iter % C.adapt_every == 0) {
+        const double pr = pri_s / (dmax(nz_s, nax_s) + 1e-10);
+        const double dr = dua_s / (dmax(naty_s, npx_s) + 1e-10);
+        double est = Rh.rho * sqrt(pr / (dr + 1e-10));
+        est = dmin(dmax(est, 1e-6), 1e6);
+        if (est > Rh.rho * C.adapt_tol || est < Rh.rho / C.adapt_tol) {
+          Rh = RhoSet(est);
+          refactor = true;
+        }
+      }
+      cta::bar();
+    }
+  }
+  if (iter > C.max_iter) iter = C.max_iter;
+  if (status == ST_UNSOLVED) status = ST_MAX_ITER;
+
+  // ---- retrieve_result (MPC.cpp:569-599) + state carried to the next call
+  cta::bar();
+  const bool bad = (status == ST_NON_CVX);
+  const double nanv = nan("");
+  if (isv) {
+    out[12 + j + 24 * k] = bad ? nanv : R.dF * R.xf;
+    out[j + 24 * k] = bad ? nanv : (R.dX * R.xX + xref[j + 12 * (1 + k)]);
+    st_d[ST_X + gvar(k, j)] = bad ? 0.0 : R.xf;
+    st_d[ST_X + gvar(k, 12 + j)] = bad ? 0.0 : R.xX;
+    st_d[ST_Z + grow(k, j)] = bad ? 0.0 : R.z1;
+    st_d[ST_Y + grow(k, j)] = bad ? 0.0 : R.y1;
+    st_d[ST_Z + grow(k, 12 + j)] = 0.0;
+    st_d[ST_Y + grow(k, 12 + j)] = bad ? 0.0 : R.y2;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+      st_d[ST_Z + grow(k, 24 + 5 * cf + q)] = bad ? 0.0 : R.q[q];
+      st_d[ST_Y + grow(k, 24 + 5 * cf + q)] = bad ? 0.0 : R.q[5 + q];
+    }
+  }
+  for (int i = tid; i < 576; i += NT) st_d[ST_BANG + i] = S.rec[SR * (i / 36) + R_BANG + (i % 36)];
+  if (tid < 32) st_i[tid] = gait[tid];
+  if (tid < NS) st_i[32 + tid] = sb[tid];
+  if (tid == 0) {
+    st_d[ST_RHO] = Rh.rho;
+    info[0] = iter;
+    info[1] = status;
+    info[2] = n_factor;
+    info[3] = overrun;
+    if (rho_out) *rho_out = Rh.rho;
+  }
+  cta::bar();
+}
+}  // namespace v2
+}  // namespace qrw

@@ -18,6 +18,7 @@
 #include "../../include/qrw_b200.h"
 #include "mpc_core.cuh"
 #include "mpc_cta_core.cuh"
+#include "mpc_v2_core.cuh"
 #include "wbc_core.cuh"
 
 using namespace qrw;
@@ -77,6 +78,32 @@ __global__ void __launch_bounds__(cta::NT, 2) mpc_cta_kernel(const MpcConst C, c
     cta::mpc_cta_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
                        st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
                        out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+    __syncthreads();
+  }
+}
+
+// Force-first CTA-per-instance MPC solve (mpc_v2_core.cuh): persistent grid of 256-thread CTAs, two per SM
+// (128 registers per thread: at 80 the per-thread solver state spilled to local memory and the long-scoreboard
+// stalls of those reloads dominated, profiles/r01_ncu_mpc_v2*.txt), pulling instance indices from the global
+// work counter.  The
+// warp that runs the sequential state recurrences differs between the CTAs that share an SM, so that they
+// do not pile up on one SM sub-partition.
+__global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, const int B, const int first,
+                                                           const int sms, const double* __restrict__ xref,
+                                                           const double* __restrict__ fsteps, double* st_d,
+                                                           int* st_i, double* out, int* info, double* rho,
+                                                           double* dbg, int* counter) {
+  extern __shared__ __align__(16) double slab[];
+  int* next = reinterpret_cast<int*>(slab + v2::V_INT) + 127;
+  const int recw = (blockIdx.x / sms) & 3;
+  for (;;) {
+    if (threadIdx.x == 0) *next = atomicAdd(counter, 1);
+    __syncthreads();
+    const int b = *next;
+    if (b >= B) break;
+    v2::mpc_v2_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
+                     st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                     out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw);
     __syncthreads();
   }
 }
@@ -208,7 +235,7 @@ struct qrw_mpc {
   int B, n_steps, N_gait, device, sms;
   MpcConst C;
   bool dbg_on = false;
-  int variant = 1;  // 1 = CTA per instance (mpc_cta_kernel), 0 = warp per instance (mpc_solve_kernel)
+  int variant = 2;  // 2 = force-first CTA kernel (mpc_v2_kernel), 1 = v1 CTA kernel, 0 = warp per instance
   double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr;
@@ -308,6 +335,7 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
+  CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
   *out = h;
   return 0;
 }
@@ -339,7 +367,13 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
-  if (h->variant == 1) {
+  if (h->variant == 2) {
+    int grid = 2 * h->sms;  // two CTAs (16 warps, 128 registers per thread) per SM
+    if (grid > h->B) grid = h->B;
+    mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, h->sms, d_xref, d_fsteps,
+                                                          h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+  } else if (h->variant == 1) {
     int grid = 2 * h->sms;  // two 84 KB slabs (16 warps) per SM
     if (grid > h->B) grid = h->B;
     mpc_cta_kernel<<<grid, cta::NT, cta::CTA_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
@@ -434,7 +468,8 @@ int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
 }
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant) {
   if (!h) return fail("qrw_mpc_set_kernel: null handle");
-  if (variant != 0 && variant != 1) return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance) or 1 (CTA per instance)");
+  if (variant < 0 || variant > 2)
+    return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance), 1 (CTA per instance, v1) or 2 (force-first CTA)");
   h->variant = variant;
   return 0;
 }

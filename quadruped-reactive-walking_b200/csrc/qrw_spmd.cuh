@@ -81,6 +81,20 @@ __device__ __forceinline__ void gather12(double v, double* out) {
   for (int j = 0; j < 12; ++j) out[j] = __shfl_sync(0xffffffffu, v, j);
 }
 __device__ __forceinline__ int fetch_add(int* p, int v) { return atomicAdd(p, v); }
+// value held by lane `src` (0..15) of the caller's 16-lane group
+__device__ __forceinline__ double shfl16(double v, int src) { return __shfl_sync(0xffffffffu, v, src, 16); }
+__device__ __forceinline__ double shfl_xor(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+// v[0..11] = p[0..11] from shared memory (16-byte aligned) as six LDS.128 issued back to back: volatile, so
+// that ptxas keeps them together ahead of their consumers instead of serialising load -> FMA -> load.
+__device__ __forceinline__ void lds12(const double* p, double* v) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+#pragma unroll
+  for (int i = 0; i < 12; i += 2)
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
+}
+// Scheduling fence for ptxas: a warp barrier is never crossed by its instruction scheduler, so the loads issued
+// before it stay grouped ahead of the arithmetic that follows (costs one issue slot).
+__device__ __forceinline__ void sched_fence() { __syncwarp(); }
 }  // namespace cta
 }  // namespace qrw
 #else
@@ -93,6 +107,12 @@ double shfl(double v, int src);
 double warp_max(double v);
 void gather12(double v, double* out);
 int fetch_add(int* p, int v);
+double shfl16(double v, int src);
+double shfl_xor(double v, int m);
+inline void sched_fence() {}
+inline void lds12(const double* p, double* v) {
+  for (int i = 0; i < 12; ++i) v[i] = p[i];
+}
 }  // namespace cta
 }  // namespace qrw
 #endif

@@ -161,6 +161,24 @@ inline void gather12(double v, double* out) {
   for (int j = 0; j < 12; ++j) out[j] = e->xch[w0 + j];
   wsync();
 }
+inline double shfl16(double v, int src) {
+  Emu* e = g_emu;
+  const int t = e->cur;
+  e->xch[t] = v;
+  wsync();
+  const double r = e->xch[(t & ~15) + (src & 15)];
+  wsync();
+  return r;
+}
+inline double shfl_xor(double v, int m) {
+  Emu* e = g_emu;
+  const int t = e->cur;
+  e->xch[t] = v;
+  wsync();
+  const double r = e->xch[(t & ~31) + ((t ^ m) & 31)];
+  wsync();
+  return r;
+}
 inline int fetch_add(int* p, int v) {
   const int o = *p;
   *p = o + v;

@@ -8,6 +8,7 @@
 
 #include "cta_emu.hpp"
 #include "../../quadruped-reactive-walking_b200/csrc/mpc_cta_core.cuh"
+#include "../../quadruped-reactive-walking_b200/csrc/mpc_v2_core.cuh"
 
 using namespace qrw;
 
@@ -88,6 +89,32 @@ extern "C" void emu_mpc_cta_run(int B, double dt, int N_gait, int first, int max
         cta::mpc_cta_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
                            st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
                            out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr);
+      });
+    }
+  };
+  if (nthreads <= 1) {
+    nthreads = 1;
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+    for (auto& t : th) t.join();
+  }
+}
+
+// Force-first CTA kernel core (csrc/mpc_v2_core.cuh), every thread of the 256-thread CTA a fiber; same contract.
+extern "C" void emu_mpc_v2_run(int B, double dt, int N_gait, int first, int max_iter, const double* xref,
+                               const double* fsteps, double* st_d, int* st_i, double* out, int* info, double* rho,
+                               double* dbg, int nthreads) {
+  MpcConst C = make_mpc_const(dt, N_gait);
+  if (max_iter > 0) C.max_iter = max_iter;
+  auto work = [&](int t) {
+    std::vector<double> slab(v2::V2_SLAB_DOUBLES, 0.0);
+    for (int b = t; b < B; b += nthreads) {
+      cta::run_cta(v2::NT, [&]() {
+        v2::mpc_v2_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
+                         st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                         out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8);
       });
     }
   };

@@ -16,10 +16,11 @@ def _p(a):
 
 
 class EmuMPC:
-    def __init__(self, emu, B, N_gait=20, core="cta"):
+    def __init__(self, emu, B, N_gait=20, core="v2"):
         self.L, self.B, self.N_gait = emu, B, N_gait
         # "cta": csrc/mpc_cta_core.cuh (256-thread CTA per instance); "warp": csrc/mpc_core.cuh
-        self.fn = emu.emu_mpc_cta_run if core == "cta" else emu.emu_mpc_run
+        # "v2": csrc/mpc_v2_core.cuh (force-first elimination, the default kernel)
+        self.fn = {"v2": emu.emu_mpc_v2_run, "cta": emu.emu_mpc_cta_run, "warp": emu.emu_mpc_run}[core]
         self.std = np.zeros((B, emu.emu_mpc_state_doubles()))
         self.sti = np.zeros((B, emu.emu_mpc_state_ints()), np.int32)
         self.out = np.zeros((B, 384))
@@ -46,7 +47,7 @@ class EmuMPC:
         return s
 
 
-@pytest.mark.parametrize("core", ["cta", "warp"])
+@pytest.mark.parametrize("core", ["v2", "cta", "warp"])
 @pytest.mark.parametrize("gaits,seed", [(("trot",), 1), (GAITS, 2)])
 def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
     from qrw_b200 import workloads as wl
@@ -72,7 +73,7 @@ def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
         x0 = ro[:, :12].copy()
 
 
-@pytest.mark.parametrize("core", ["cta", "warp"])
+@pytest.mark.parametrize("core", ["v2", "cta", "warp"])
 def test_mpc_scaling_and_bounds(emu, oracle, core):
     from qrw_b200 import workloads as wl
 
@@ -93,7 +94,7 @@ def test_mpc_scaling_and_bounds(emu, oracle, core):
         x0 = o.get_latest_result()[:, :12].copy()
 
 
-@pytest.mark.parametrize("core", ["cta", "warp"])
+@pytest.mark.parametrize("core", ["v2", "cta", "warp"])
 def test_mpc_flight_phase_and_stale_rows(emu, oracle, core):
     """Quirk A.6-2: an all-swing fsteps row terminates gait processing; later steps keep the stale
     B / S values of earlier calls."""
@@ -112,7 +113,7 @@ def test_mpc_flight_phase_and_stale_rows(emu, oracle, core):
         assert_forces_close(e.out, o.get_latest_result(), f"run({k})")
 
 
-@pytest.mark.parametrize("core", ["cta", "warp"])
+@pytest.mark.parametrize("core", ["v2", "cta", "warp"])
 def test_mpc_max_iter_returns_last_iterate(emu, oracle, core):
     """Quirk A.6-8: on max_iter the last iterate is returned (status -2 / 2), never an error."""
     from qrw_b200 import workloads as wl

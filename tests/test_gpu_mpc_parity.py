@@ -8,7 +8,7 @@ from conftest import assert_forces_close
 pytestmark = pytest.mark.gpu
 
 
-def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=1):
+def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=2):
     from qrw_b200 import BatchedMPC, workloads as wl
 
     w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
@@ -26,7 +26,7 @@ def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=1):
         ig, ic = gpu.info(), cpu.info()
         assert np.array_equal(ig["iters"], ic["iters"]), f"ADMM iteration counts differ at tick {t}"
         assert np.array_equal(ig["status"], ic["status"])
-        np.testing.assert_allclose(ig["rho"], ic["rho"], rtol=1e-6)
+        np.testing.assert_allclose(ig["rho"], ic["rho"], rtol=1e-4)  # sqrt of a ratio of 1e-6-sized residuals
         R = rg.reshape(B, 16, 24)
         C = rc.reshape(B, 16, 24)
         assert_forces_close(R[:, :, 12:], C[:, :, 12:], f"forces, tick {t}")
@@ -52,26 +52,27 @@ def test_config1_single_trot(oracle):
     assert np.abs(f[0, 3:9]).max() < 1e-4
 
 
-@pytest.mark.parametrize("kernel", [1, 0])
+@pytest.mark.parametrize("kernel", [2, 1, 0])
 def test_trot_batch_closed_loop(oracle, kernel):
     _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4, kernel=kernel)
 
 
-@pytest.mark.parametrize("kernel", [1, 0])
+@pytest.mark.parametrize("kernel", [2, 1, 0])
 def test_mixed_gaits_closed_loop(oracle, kernel):
     _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3, kernel=kernel)
 
 
-def test_kernel_variants_agree_at_full_size():
-    """4096 trot instances, cold tick + one update tick: the CTA-per-instance kernel and the warp-per-instance
-    kernel follow the same iterate sequence (same iteration counts, results equal to round-off)."""
+@pytest.mark.parametrize("va,vb", [(2, 1), (1, 0)])
+def test_kernel_variants_agree_at_full_size(va, vb):
+    """4096 trot instances, cold tick + one update tick: the kernel variants (2 = force-first CTA, 1 = v1 CTA,
+    0 = warp per instance) follow the same iterate sequence (same iteration counts, results equal to round-off)."""
     from qrw_b200 import BatchedMPC, workloads as wl
 
     B = 4096
     w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=3)
     a, b = BatchedMPC(B), BatchedMPC(B)
-    a.set_kernel(1)
-    b.set_kernel(0)
+    a.set_kernel(va)
+    b.set_kernel(vb)
     x0 = None
     for t in range(2):
         xr, fs = w.inputs(t, x0)
@@ -80,7 +81,7 @@ def test_kernel_variants_agree_at_full_size():
         ra, rb = a.get_latest_result(), b.get_latest_result()
         same = a.info()["iters"] == b.info()["iters"]
         assert same.mean() > 0.995, f"tick {t}: {(~same).sum()} instances differ in iteration count"
-        assert np.abs(ra[same] - rb[same]).max() < 1e-7
+        assert np.abs(ra[same] - rb[same]).max() < 1e-6
         assert np.abs(ra - rb).max() < 1e-4
         x0 = ra[:, :12].copy()
 

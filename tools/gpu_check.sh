@@ -15,6 +15,6 @@ timeout 300 $SMALL > $OUT/small.json 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/launches.csv $SMALL > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?" | tee -a $OUT/rc.txt
 timeout 300 $SMALL > $OUT/small2.json 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:mpc_cta_kernel -s 6 -c 1 -f -o $OUT/prof_mpc $SMALL > $OUT/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:mpc_v2_kernel -s 6 -c 1 -f -o $OUT/prof_mpc $SMALL > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?" | tee -a $OUT/rc.txt
 ls -la $OUT
