@@ -44,10 +44,12 @@ constexpr int R_D = 112;   // [24] Ruiz column scaling: 0..11 force, 12..23 stat
 constexpr int R_E = 136;   // [44] Ruiz row scaling: 12 dyn | 12 enable | 20 cone
 constexpr int R_BANG = 180;  // [3][12] angular block of B_k (unscaled)
 constexpr int R_B1 = 216;  // [12] scaled right-hand side of the dynamics rows
-constexpr int SR = 228;
+constexpr int R_GF = 228;  // [6][14] rows 6..11 of GF = E B0 D_f F^-1 (what the dynamics rows see of a force right-hand side)
+constexpr int R_MR = 312;  // [6][6]  M = GF D_f B0' E (rows 6..11 x rows 6..11)
+constexpr int SR = 348;
 constexpr int V_W = V_REC + 16 * SR;  // [144] Gauss-Jordan ping-pong / T_k staging of the factorisation
-constexpr int V_SAVE = V_W + 144;     // [23][32] registers of the recurrence warp, parked while it runs the chain
-constexpr int V_RED = V_SAVE + 736;   // 128   reductions
+constexpr int V_SAVE = V_W + 144;     // [33][32] registers of the recurrence warp, parked while it runs the chain
+constexpr int V_RED = V_SAVE + 1056;  // 128   reductions
 constexpr int V_INT = V_RED + 128;    // 128 ints
 constexpr int V2_SLAB_DOUBLES = V_INT + 64;
 constexpr int V2_SLAB_BYTES = V2_SLAB_DOUBLES * 8;
@@ -68,12 +70,15 @@ struct Sm {
 
 QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
 
-// per-thread registers.  q[] is role-dependent so that both roles fit the same 15 doubles:
-//   variable lane (j < 12): q[0..11] = row j of F_k^-1, q[12..14] = B_k(9..11, j)
-//   cone lane (j >= 12)   : q[0..4] = z, q[5..9] = y, q[10..14] = E of the foot's five cone rows
+// per-thread registers of variable lane j = 3 foot + axis of stage k (lanes 12..15 of a stage idle):
+//   q[0..11] = row j of F_k^-1, q[12..14] = B_k(9..11, j), gf[0..5] = column j of GF (rows 6..11)
+//   xf, xX: scaled iterates of f_k[j], X_{k+1}[j]; z1, y1, e1: dynamics row (k,j); y2: force-enable row (k,j)
+//   friction-cone rows of the foot, two slots: axis x -> rows 0,1 (+-fx - mu fz), axis y -> rows 2,3, axis z -> row 4 (-fz)
+//   in slot A and nothing in slot B
 struct Regs {
-  double q[15];
+  double q[15], gf[6];
   double xf, xX, dF, dX, z1, y1, e1, y2;
+  double zA, yA, eA, zB, yB, eB;
 };
 
 // unscaled dynamics row 6+r (r = 0..5) of a stage applied to a force-space vector v[0..11] held in shared memory
@@ -185,7 +190,12 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
       y[5] += Bk[24 + b] * fd;
     }
 #pragma unroll
-    for (int r = 0; r < 6; ++r) Y[6 * j + r] = y[r];
+    for (int r = 0; r < 6; ++r) {
+      Y[6 * j + r] = y[r];
+      const double g = Ek[6 + r] * y[r];  // GF(6+r, j) = E (B0 D_f F^-1)(6+r, j), F^-1 symmetric
+      R.gf[r] = g;
+      rec[R_GF + LD * r + j] = g;
+    }
   }
   cta::wsync();
   // N_k(r, r') = e_r^2 e_r'^2 sum_a B0(6+r, a) D_f(a) Y(a, r'); three entries per variable lane
@@ -203,6 +213,7 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
       }
       const double er = Ek[6 + r], erp = Ek[6 + rp];
       nv[t] = (er * er) * acc * (erp * erp);
+      rec[R_MR + e] = er * acc * erp;
     }
   }
   cta::wsync();  // N overlaps the tail of Y: everybody has read Y
@@ -404,7 +415,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   Regs R;
   const bool isv = j < 12;
   const int c3 = j % 3, ft = isv ? j / 3 : 0;
-  const int cf = isv ? 0 : j - 12;  // foot of a cone lane
+  // friction-cone rows owned by this lane (stage-local row index; slot B only for the x and y axes)
+  const int rowA = 24 + 5 * ft + (c3 < 2 ? 2 * c3 : 4);
+  const bool hasB = isv && c3 < 2;
   double* rec = S.rec + SR * k;
   double* BAk = rec + R_BA;
   double* BBk = rec + R_BB;
@@ -420,20 +433,20 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   if (tid < NS) sb[tid] = first ? 0 : st_i[32 + tid];
 #pragma unroll
   for (int t = 0; t < 15; ++t) R.q[t] = 0.0;
-  R.xf = R.xX = R.z1 = R.y1 = R.y2 = 0.0;
-  if (!first) {
-    if (isv) {
-      R.xf = st_d[ST_X + gvar(k, j)];
-      R.xX = st_d[ST_X + gvar(k, 12 + j)];
-      R.z1 = st_d[ST_Z + grow(k, j)];
-      R.y1 = st_d[ST_Y + grow(k, j)];
-      R.y2 = st_d[ST_Y + grow(k, 12 + j)];
-    } else {
 #pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        R.q[q] = st_d[ST_Z + grow(k, 24 + 5 * cf + q)];
-        R.q[5 + q] = st_d[ST_Y + grow(k, 24 + 5 * cf + q)];
-      }
+  for (int t = 0; t < 6; ++t) R.gf[t] = 0.0;
+  R.xf = R.xX = R.z1 = R.y1 = R.y2 = R.zA = R.yA = R.zB = R.yB = 0.0;
+  if (!first && isv) {
+    R.xf = st_d[ST_X + gvar(k, j)];
+    R.xX = st_d[ST_X + gvar(k, 12 + j)];
+    R.z1 = st_d[ST_Z + grow(k, j)];
+    R.y1 = st_d[ST_Y + grow(k, j)];
+    R.y2 = st_d[ST_Y + grow(k, 12 + j)];
+    R.zA = st_d[ST_Z + grow(k, rowA)];
+    R.yA = st_d[ST_Y + grow(k, rowA)];
+    if (hasB) {
+      R.zB = st_d[ST_Z + grow(k, rowA + 1)];
+      R.yB = st_d[ST_Y + grow(k, rowA + 1)];
     }
   }
   double rho_now = first ? C.rho0 : st_d[ST_RHO];
@@ -536,18 +549,14 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   }
   // Ruiz start values
   double e2 = 1.0;
-  R.dF = R.dX = R.e1 = 1.0;
+  R.dF = R.dX = R.e1 = R.eA = R.eB = 1.0;
   if (isv) {
     Dk[j] = 1.0;
     Dk[12 + j] = 1.0;
     Ek[j] = 1.0;
     Ek[12 + j] = 1.0;
-  } else {
-#pragma unroll
-    for (int q = 0; q < 5; ++q) {
-      R.q[10 + q] = 1.0;
-      Ek[24 + 5 * cf + q] = 1.0;
-    }
+    Ek[rowA] = 1.0;
+    if (hasB) Ek[rowA + 1] = 1.0;
   }
   cta::bar();
   if (isv) {
@@ -560,7 +569,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   // ---- Ruiz equilibration, 10 passes (OSQP scale_data; rerun on every call, MPC.cpp:541,548)
   double cscale = 1.0;
   for (int pass = 0; pass < 10; ++pass) {
-    double dDF = 1.0, dDX = 1.0, dE1 = 1.0, dE2 = 1.0, dEc[5];
+    double dDF = 1.0, dDX = 1.0, dE1 = 1.0, dE2 = 1.0, dEA = 1.0, dEB = 1.0;
     if (isv) {
       const int i = j;
       // column of f_k[j]
@@ -572,14 +581,12 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       nrm = dmax(nrm, fabs(R.q[14]) * Ek[11] * d);
       if (bit) nrm = dmax(nrm, e2 * d);
       const double* Ec = Ek + 24 + 5 * ft;
-      if (c3 == 0) {
-        nrm = dmax(nrm, dmax(Ec[0], Ec[1]) * d);
-      } else if (c3 == 1) {
-        nrm = dmax(nrm, dmax(Ec[2], Ec[3]) * d);
+      if (c3 < 2) {
+        nrm = dmax(nrm, dmax(R.eA, R.eB) * d);
       } else {
         const double em = dmax(dmax(Ec[0], Ec[1]), dmax(Ec[2], Ec[3]));
         nrm = dmax(nrm, C.mu * em * d);
-        nrm = dmax(nrm, Ec[4] * d);
+        nrm = dmax(nrm, R.eA * d);
       }
       dDF = 1.0 / sqrt(limit_scaling(nrm));
       // column of X_{k+1}[i]
@@ -609,13 +616,13 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       dE1 = 1.0 / sqrt(limit_scaling(nr));
       const double nf = bit ? e2 * d : 0.0;
       dE2 = 1.0 / sqrt(limit_scaling(nf));
-    } else {
-      const double* Df = Dk + 3 * cf;
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        const double e = R.q[10 + q];
-        const double nr = (q == 4) ? e * Df[2] : dmax(e * Df[q >> 1], C.mu * e * Df[2]);
-        dEc[q] = 1.0 / sqrt(limit_scaling(nr));
+      // friction-cone rows of this lane
+      const double dz = Dk[3 * ft + 2];
+      if (c3 < 2) {
+        dEA = 1.0 / sqrt(limit_scaling(dmax(R.eA * d, C.mu * R.eA * dz)));
+        dEB = 1.0 / sqrt(limit_scaling(dmax(R.eB * d, C.mu * R.eB * dz)));
+      } else {
+        dEA = 1.0 / sqrt(limit_scaling(R.eA * d));
       }
     }
     cta::bar();
@@ -625,17 +632,15 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       R.dX *= dDX;
       R.e1 *= dE1;
       e2 *= dE2;
+      R.eA *= dEA;
+      R.eB *= dEB;
       Dk[j] = R.dF;
       Dk[12 + j] = R.dX;
       Ek[j] = R.e1;
       Ek[12 + j] = e2;
+      Ek[rowA] = R.eA;
+      if (hasB) Ek[rowA + 1] = R.eB;
       psum = fabs(cscale * C.wf * R.dF * R.dF) + fabs(cscale * C.w[j] * R.dX * R.dX);
-    } else {
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        R.q[10 + q] *= dEc[q];
-        Ek[24 + 5 * cf + q] = R.q[10 + q];
-      }
     }
     // cost normalisation: mean of the column norms of the scaled P (diagonal)
 #pragma unroll
@@ -652,21 +657,21 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   }
   cta::bar();
   const double cinv = 1.0 / cscale;
-  if (dbg) {
-    if (isv) {
-      dbg[gvar(k, j)] = R.dF;
-      dbg[gvar(k, 12 + j)] = R.dX;
-      dbg[NX + grow(k, j)] = R.e1;
-      dbg[NX + grow(k, 12 + j)] = e2;
-    } else {
-#pragma unroll
-      for (int q = 0; q < 5; ++q) dbg[NX + grow(k, 24 + 5 * cf + q)] = R.q[10 + q];
-    }
+  if (dbg && isv) {
+    dbg[gvar(k, j)] = R.dF;
+    dbg[gvar(k, 12 + j)] = R.dX;
+    dbg[NX + grow(k, j)] = R.e1;
+    dbg[NX + grow(k, 12 + j)] = e2;
+    dbg[NX + grow(k, rowA)] = R.eA;
+    if (hasB) dbg[NX + grow(k, rowA + 1)] = R.eB;
     if (tid == 0) dbg[NX + NR] = cscale;
   }
   if (isv) rec[R_B1 + j] = R.e1 * bnd;
+  // the axis-z lane's row 4 is the only cone row with a finite lower bound (-25 E); OSQP makes it an equality
+  // row (rho_eq) when the scaled width drops under RHO_TOL
+  const bool eq4 = isv && c3 == 2 && (25.0 * R.eA < 1e-4);
 
-  // ---- KKT factorisation
+  // ---- KKT factorisation (inside the loop: first iteration and after every rho update)
   RhoSet Rh(rho_now);
   int n_factor = 0;
   bool refactor = true;
@@ -675,71 +680,73 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   int status = ST_UNSOLVED;
   int iter = 0;
   for (iter = 1; iter <= C.max_iter; ++iter) {
-    if (refactor) {  // first iteration and after every rho update (single inlined call site)
+    if (refactor) {
       factor(C, S, R, Rh, cscale, tid);
       ++n_factor;
       refactor = false;
     }
-    // (1) row values u = E (rho z - y); cone lanes hand the foot's A' contribution to the force owners
-    double u1 = 0.0, u2 = 0.0;
+    const double rhoA = eq4 ? Rh.rho_eq : Rh.rho, rinvA = eq4 ? Rh.rinv_eq : Rh.rinv;
+    // (1) row values u = E (rho z - y); pair sums of the cone rows for the axis-z lane of the foot
+    double u1 = 0.0, u2 = 0.0, uA = 0.0, uB = 0.0;
     if (isv) {
       u1 = R.e1 * (Rh.rho_eq * R.z1 - R.y1);
       if (bit) u2 = Ek[12 + j] * (Rh.rho_eq * 0.0 - R.y2);
+      uA = R.eA * (rhoA * R.zA - R.yA);
+      uB = R.eB * (Rh.rho * R.zB - R.yB);
       BAk[j] = u1;
-    } else {
-      double uc[5];
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        const bool eq = (q == 4) && (25.0 * R.q[14] < 1e-4);
-        uc[q] = R.q[10 + q] * ((eq ? Rh.rho_eq : Rh.rho) * R.q[q] - R.q[5 + q]);
-      }
-      BDk[3 * cf] = uc[0] - uc[1];
-      BDk[3 * cf + 1] = uc[2] - uc[3];
-      BDk[3 * cf + 2] = -C.mu * (uc[0] + uc[1] + uc[2] + uc[3]) - uc[4];
+      BDk[j] = uA + uB;
     }
     cta::wsync();
     // (2) t_f = sigma x_f + D_f (A' u)_f
-    double tf = 0.0;
     if (isv) {
       double v = C.dtm * BAk[6 + c3];
       v += R.q[12] * BAk[9];
       v += R.q[13] * BAk[10];
       v += R.q[14] * BAk[11];
       if (bit) v += u2;
-      v += BDk[j];
-      tf = C.sigma * R.xf + R.dF * v;
-      BBk[j] = tf;
+      if (c3 < 2)
+        v += uA - uB;
+      else
+        v += -C.mu * (BDk[3 * ft] + BDk[3 * ft + 1]) - uA;
+      BBk[j] = C.sigma * R.xf + R.dF * v;
     }
     cta::wsync();
-    // (3) u_f = F^-1 t_f
-    double uf = 0.0;
+    // (3) u_f = F^-1 t_f and w = GF t_f (rows 6..11) from the same broadcast of t_f;
+    //     m = u - rho E w: what the state system sees of the dynamics rows; A_k = sigma x_X - D_X m_k
+    double uf = 0.0, wv = 0.0, mk = 0.0;
     if (isv) {
+      double tv[12];
+      cta::lds12(BBk, tv);
       double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
       for (int b = 0; b < 12; b += 4) {
-        a0 += R.q[b] * BBk[b];
-        a1 += R.q[b + 1] * BBk[b + 1];
-        a2 += R.q[b + 2] * BBk[b + 2];
-        a3 += R.q[b + 3] * BBk[b + 3];
+        a0 += R.q[b] * tv[b];
+        a1 += R.q[b + 1] * tv[b + 1];
+        a2 += R.q[b + 2] * tv[b + 2];
+        a3 += R.q[b + 3] * tv[b + 3];
       }
       uf = (a0 + a1) + (a2 + a3);
-      BAk[j] = R.dF * uf;
-    }
-    cta::wsync();
-    // (4) m = u - rho E (B0 D_f u_f): what the state system sees of the dynamics rows;
-    //     A_k = sigma x_X - D_X m_k (own record), CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
-    double mk = 0.0;
-    if (isv) {
-      double wv = 0.0;
-      if (j >= 6) wv = R.e1 * b0_row(C, Bk, BAk, j - 6);
+      if (j >= 6) {
+        const double* g = rec + R_GF + LD * (j - 6);
+        double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+#pragma unroll
+        for (int b = 0; b < 12; b += 4) {
+          b0 += g[b] * tv[b];
+          b1 += g[b + 1] * tv[b + 1];
+          b2 += g[b + 2] * tv[b + 2];
+          b3 += g[b + 3] * tv[b + 3];
+        }
+        wv = (b0 + b1) + (b2 + b3);
+      }
       mk = u1 - Rh.rho_eq * (R.e1 * wv);
-      BBk[j] = mk;
+      BAk[j] = mk;
       rec[R_A + j] = C.sigma * R.xX - R.dX * mk;
     }
     cta::wsync();
+    // (4) CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
     if (isv && k > 0) {
       double v = mk;
-      if (j >= 6) v += C.dt * BBk[j - 6];
+      if (j >= 6) v += C.dt * BAk[j - 6];
       rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
     }
     cta::bar();
@@ -749,117 +756,116 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       double* sv = S.save + l;
 #pragma unroll
       for (int t = 0; t < 15; ++t) sv[32 * t] = R.q[t];
-      sv[32 * 15] = R.xf;
-      sv[32 * 16] = R.xX;
-      sv[32 * 17] = R.z1;
-      sv[32 * 18] = R.y1;
-      sv[32 * 19] = R.y2;
-      sv[32 * 20] = uf;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) sv[32 * (15 + t)] = R.gf[t];
+      sv[32 * 21] = R.xf;
+      sv[32 * 22] = R.xX;
+      sv[32 * 23] = R.z1;
+      sv[32 * 24] = R.y1;
+      sv[32 * 25] = R.y2;
+      sv[32 * 26] = R.zA;
+      sv[32 * 27] = R.yA;
+      sv[32 * 28] = R.zB;
+      sv[32 * 29] = R.yB;
+      sv[32 * 30] = uf;
+      sv[32 * 31] = wv;
       state_recurrence(S, l);
 #pragma unroll
       for (int t = 0; t < 15; ++t) R.q[t] = sv[32 * t];
-      R.xf = sv[32 * 15];
-      R.xX = sv[32 * 16];
-      R.z1 = sv[32 * 17];
-      R.y1 = sv[32 * 18];
-      R.y2 = sv[32 * 19];
-      uf = sv[32 * 20];
+#pragma unroll
+      for (int t = 0; t < 6; ++t) R.gf[t] = sv[32 * (15 + t)];
+      R.xf = sv[32 * 21];
+      R.xX = sv[32 * 22];
+      R.z1 = sv[32 * 23];
+      R.y1 = sv[32 * 24];
+      R.y2 = sv[32 * 25];
+      R.zA = sv[32 * 26];
+      R.yA = sv[32 * 27];
+      R.zB = sv[32 * 28];
+      R.yB = sv[32 * 29];
+      uf = sv[32 * 30];
+      wv = sv[32 * 31];
       if (isv) {
         R.dF = Dk[j];
         R.dX = Dk[12 + j];
         R.e1 = Ek[j];
+        R.eA = Ek[rowA];
+        if (hasB) R.eB = Ek[rowA + 1];
       }
     }
     cta::bar();
-    // (5) dynamics rows applied to the new states; h = rho D_f B0' E^2 (...)
-    double xtX = 0.0, smX = 0.0;
+    // (5) dynamics rows applied to the new states: r = E (-D_X x~_X + A D_X x~_X^{k-1})
+    double xtX = 0.0, rX = 0.0;
     if (isv) {
       xtX = rec[R_XT + j];
-      smX = -(R.dX * xtX);
+      double smX = -(R.dX * xtX);
       if (k > 0) {
         smX += Dk[-SR + 12 + j] * rec[-SR + R_XT + j];
         if (j < 6) smX += C.dt * (Dk[-SR + 18 + j] * rec[-SR + R_XT + j + 6]);
       }
-      BAk[j] = R.e1 * (R.e1 * smX);
+      rX = R.e1 * smX;
+      BAk[j] = rX;
     }
     cta::wsync();
+    // (6) x~_f = u_f - rho GF' r ;  z~ (dynamics rows) = r + w - rho M r
+    double xtf = 0.0, zt = rX;
     if (isv) {
-      double v = C.dtm * BAk[6 + c3];
-      v += R.q[12] * BAk[9];
-      v += R.q[13] * BAk[10];
-      v += R.q[14] * BAk[11];
-      BBk[j] = Rh.rho_eq * (R.dF * v);
-    }
-    cta::wsync();
-    // (6) x~_f = u_f - F^-1 h
-    double xtf = 0.0;
-    if (isv) {
-      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll
-      for (int b = 0; b < 12; b += 4) {
-        a0 += R.q[b] * BBk[b];
-        a1 += R.q[b + 1] * BBk[b + 1];
-        a2 += R.q[b + 2] * BBk[b + 2];
-        a3 += R.q[b + 3] * BBk[b + 3];
-      }
-      xtf = uf - ((a0 + a1) + (a2 + a3));
+      const double r0 = BAk[6], r1 = BAk[7], r2 = BAk[8], r3 = BAk[9], r4 = BAk[10], r5 = BAk[11];
+      const double s0 = (R.gf[0] * r0 + R.gf[1] * r1) + (R.gf[2] * r2 + R.gf[3] * r3) + (R.gf[4] * r4 + R.gf[5] * r5);
+      xtf = uf - Rh.rho_eq * s0;
       BCk[j] = R.dF * xtf;
+      if (j >= 6) {
+        const double* Mr = rec + R_MR + 6 * (j - 6);
+        const double s1 = (Mr[0] * r0 + Mr[1] * r1) + (Mr[2] * r2 + Mr[3] * r3) + (Mr[4] * r4 + Mr[5] * r5);
+        zt = rX + (wv - Rh.rho_eq * s1);
+      }
     }
     cta::wsync();
-    // (7) z~ = A x~, relaxation, projection, dual update, x update
+    // (7) relaxation, projection, dual update, x update
     if (isv) {
-      double sm = smX;
-      if (j >= 6) sm += b0_row(C, Bk, BCk, j - 6);
-      const double zt = R.e1 * sm;
       const double zr = C.alpha * zt + (1.0 - C.alpha) * R.z1;
       const double zn = rec[R_B1 + j];
       R.y1 += Rh.rho_eq * (zr - zn);
       R.z1 = zn;
       // force-enable row (k, j): l = u = 0
-      const double zt2 = bit ? Ek[12 + j] * BCk[j] : 0.0;
+      const double dxf = R.dF * xtf;
+      const double zt2 = bit ? Ek[12 + j] * dxf : 0.0;
       const double zr2 = C.alpha * zt2 + (1.0 - C.alpha) * 0.0;
       R.y2 += Rh.rho_eq * (zr2 - 0.0);
       R.xf = C.alpha * xtf + (1.0 - C.alpha) * R.xf;
       R.xX = C.alpha * xtX + (1.0 - C.alpha) * R.xX;
-    } else {
-      const double fx = BCk[3 * cf], fy = BCk[3 * cf + 1], fz = BCk[3 * cf + 2];
-      const bool eq4 = 25.0 * R.q[14] < 1e-4;
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        double row;
-        if (q == 4)
-          row = -fz;
-        else {
-          const double t = (q >> 1) ? fy : fx;
-          row = ((q & 1) ? -t : t) - C.mu * fz;
-        }
-        const bool eq = (q == 4) && eq4;
-        const double rr = eq ? Rh.rho_eq : Rh.rho, ri = eq ? Rh.rinv_eq : Rh.rinv;
-        const double e = R.q[10 + q];
-        const double zt = e * row;
-        const double zr = C.alpha * zt + (1.0 - C.alpha) * R.q[q];
-        double zn = zr + ri * R.q[5 + q];
-        if (q == 4) zn = dmax(zn, -25.0 * e);
-        zn = dmin(zn, 0.0);
-        R.q[5 + q] += rr * (zr - zn);
-        R.q[q] = zn;
+      // friction-cone rows: slot A = +f_axis - mu fz (or -fz for the z lane), slot B = -f_axis - mu fz
+      const double fz = BCk[3 * ft + 2];
+      const double rowa = (c3 < 2) ? dxf - C.mu * fz : -fz;
+      {
+        const double ztc = R.eA * rowa;
+        const double zrc = C.alpha * ztc + (1.0 - C.alpha) * R.zA;
+        double znc = zrc + rinvA * R.yA;
+        if (c3 == 2) znc = dmax(znc, -25.0 * R.eA);
+        znc = dmin(znc, 0.0);
+        R.yA += rhoA * (zrc - znc);
+        R.zA = znc;
+      }
+      if (c3 < 2) {
+        const double ztc = R.eB * (-dxf - C.mu * fz);
+        const double zrc = C.alpha * ztc + (1.0 - C.alpha) * R.zB;
+        const double znc = dmin(zrc + Rh.rinv * R.yB, 0.0);
+        R.yB += Rh.rho * (zrc - znc);
+        R.zB = znc;
       }
     }
     if (iter % C.check_every == 0) {
       // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
       cta::bar();  // everyone is done with the exchange buffers of this iteration
+      double yA = 0.0, yB = 0.0;
       if (isv) {
         BCk[j] = R.dF * R.xf;
         rec[R_XT + j] = R.dX * R.xX;
         rec[R_A + j] = R.e1 * R.y1;
         BBk[j] = Ek[12 + j] * R.y2;
-      } else {
-        double uc[5];
-#pragma unroll
-        for (int q = 0; q < 5; ++q) uc[q] = R.q[10 + q] * R.q[5 + q];
-        BDk[3 * cf] = uc[0] - uc[1];
-        BDk[3 * cf + 1] = uc[2] - uc[3];
-        BDk[3 * cf + 2] = -C.mu * (uc[0] + uc[1] + uc[2] + uc[3]) - uc[4];
+        yA = R.eA * R.yA;
+        yB = R.eB * R.yB;
+        BDk[j] = yA + yB;
       }
       cta::bar();
       double m[12];
@@ -892,6 +898,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         if (j >= 6) sm += b0_row(C, Bk, BCk, j - 6);
         row_acc(R.e1 * sm, R.z1, R.e1);
         row_acc(bit ? Ek[12 + j] * BCk[j] : 0.0, 0.0, Ek[12 + j]);
+        const double dxf = BCk[j], fz = BCk[3 * ft + 2];
+        row_acc(R.eA * ((c3 < 2) ? dxf - C.mu * fz : -fz), R.zA, R.eA);
+        if (c3 < 2) row_acc(R.eB * (-dxf - C.mu * fz), R.zB, R.eB);
         // force variable
         const double* u = rec + R_A;
         double v = C.dtm * u[6 + c3];
@@ -899,7 +908,10 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         v += R.q[13] * u[10];
         v += R.q[14] * u[11];
         if (bit) v += BBk[j];
-        v += BDk[j];
+        if (c3 < 2)
+          v += yA - yB;
+        else
+          v += -C.mu * (BDk[3 * ft] + BDk[3 * ft + 1]) - yA;
         var_acc(R.dF * v, (cscale * C.wf * R.dF * R.dF) * R.xf, R.dF);
         // state variable
         double vx = -u[j];
@@ -908,19 +920,6 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
           if (j >= 6) vx += C.dt * u[SR + j - 6];
         }
         var_acc(R.dX * vx, (cscale * C.w[j] * R.dX * R.dX) * R.xX, R.dX);
-      } else {
-        const double fx = BCk[3 * cf], fy = BCk[3 * cf + 1], fz = BCk[3 * cf + 2];
-#pragma unroll
-        for (int q = 0; q < 5; ++q) {
-          double row;
-          if (q == 4)
-            row = -fz;
-          else {
-            const double t = (q >> 1) ? fy : fx;
-            row = ((q & 1) ? -t : t) - C.mu * fz;
-          }
-          row_acc(R.q[10 + q] * row, R.q[q], R.q[10 + q]);
-        }
       }
 #pragma unroll
       for (int q = 0; q < 12; ++q) {
@@ -980,11 +979,11 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     st_d[ST_Y + grow(k, j)] = bad ? 0.0 : R.y1;
     st_d[ST_Z + grow(k, 12 + j)] = 0.0;
     st_d[ST_Y + grow(k, 12 + j)] = bad ? 0.0 : R.y2;
-  } else {
-#pragma unroll
-    for (int q = 0; q < 5; ++q) {
-      st_d[ST_Z + grow(k, 24 + 5 * cf + q)] = bad ? 0.0 : R.q[q];
-      st_d[ST_Y + grow(k, 24 + 5 * cf + q)] = bad ? 0.0 : R.q[5 + q];
+    st_d[ST_Z + grow(k, rowA)] = bad ? 0.0 : R.zA;
+    st_d[ST_Y + grow(k, rowA)] = bad ? 0.0 : R.yA;
+    if (hasB) {
+      st_d[ST_Z + grow(k, rowA + 1)] = bad ? 0.0 : R.zB;
+      st_d[ST_Y + grow(k, rowA + 1)] = bad ? 0.0 : R.yB;
     }
   }
   for (int i = tid; i < 576; i += NT) st_d[ST_BANG + i] = S.rec[SR * (i / 36) + R_BANG + (i % 36)];
@@ -1000,5 +999,6 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   }
   cta::bar();
 }
+
 }  // namespace v2
 }  // namespace qrw
