@@ -46,10 +46,10 @@ constexpr int R_BANG = 180;  // [3][12] angular block of B_k (unscaled)
 constexpr int R_B1 = 216;  // [12] scaled right-hand side of the dynamics rows
 constexpr int R_GF = 228;  // [6][14] rows 6..11 of GF = E B0 D_f F^-1 (what the dynamics rows see of a force right-hand side)
 constexpr int R_MR = 312;  // [6][6]  M = GF D_f B0' E (rows 6..11 x rows 6..11)
-constexpr int SR = 348;
+constexpr int R_FI = 348;  // [12][14] F_k^-1 (in registers it was spilled to local memory around the chain call)
+constexpr int SR = 516;
 constexpr int V_W = V_REC + 16 * SR;  // [144] Gauss-Jordan ping-pong / T_k staging of the factorisation
-constexpr int V_SAVE = V_W + 144;     // [33][32] registers of the recurrence warp, parked while it runs the chain
-constexpr int V_RED = V_SAVE + 1056;  // 128   reductions
+constexpr int V_RED = V_W + 144;      // 128   reductions
 constexpr int V_INT = V_RED + 128;    // 128 ints
 constexpr int V2_SLAB_DOUBLES = V_INT + 64;
 constexpr int V2_SLAB_BYTES = V2_SLAB_DOUBLES * 8;
@@ -58,25 +58,25 @@ constexpr int R_Y = 0;   // [12][6] F_k^-1 (D_f B0')(:, rows 6..11); dead after 
 constexpr int R_N = 72;  // [36]    N_k (6x6); dead after step (d)
 static_assert(R_N + 36 <= R_D, "factorisation scratch overruns the record");
 static_assert((SR * 8) % 16 == 0 && (V_REC * 8) % 16 == 0, "records must keep 16-byte alignment");
-static_assert(V2_SLAB_BYTES <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
+static_assert(V2_SLAB_BYTES <= 112 * 1024, "two CTAs per SM need <= 113 KB each");
 
 struct Sm {
-  double *Sig, *T, *rec, *W, *save, *red;
+  double *Sig, *T, *rec, *W, *red;
   int* ib;
   QRW_HD explicit Sm(double* b)
-      : Sig(b + V_SIG), T(b + V_T), rec(b + V_REC), W(b + V_W), save(b + V_SAVE), red(b + V_RED),
+      : Sig(b + V_SIG), T(b + V_T), rec(b + V_REC), W(b + V_W), red(b + V_RED),
         ib(reinterpret_cast<int*>(b + V_INT)) {}
 };
 
 QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
 
 // per-thread registers of variable lane j = 3 foot + axis of stage k (lanes 12..15 of a stage idle):
-//   q[0..11] = row j of F_k^-1, q[12..14] = B_k(9..11, j), gf[0..5] = column j of GF (rows 6..11)
+//   bc[0..2] = B_k(9..11, j), gf[0..5] = column j of GF (rows 6..11); row j of F_k^-1 lives in the record (R_FI)
 //   xf, xX: scaled iterates of f_k[j], X_{k+1}[j]; z1, y1, e1: dynamics row (k,j); y2: force-enable row (k,j)
 //   friction-cone rows of the foot, two slots: axis x -> rows 0,1 (+-fx - mu fz), axis y -> rows 2,3, axis z -> row 4 (-fz)
 //   in slot A and nothing in slot B
 struct Regs {
-  double q[15], gf[6];
+  double bc[3], gf[6];
   double xf, xX, dF, dX, z1, y1, e1, y2;
   double zA, yA, eA, zB, yB, eB;
 };
@@ -115,7 +115,7 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
   double* N = rec + R_N;
   double* W = S.W;
   double F[12];
-  const double b0 = R.q[12], b1 = R.q[13], b2 = R.q[14];
+  const double b0 = R.bc[0], b1 = R.bc[1], b2 = R.bc[2];
   // ---- (a) row j of F_k
   if (isv) {
     const double e6 = Ek[6 + c3], e9 = Ek[9], e10 = Ek[10], e11 = Ek[11];
@@ -179,7 +179,7 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
   // ---- (c) Y(j, r) = sum_b Finv(j,b) D_f(b) B0(6+r, b), r = 0..5
   if (isv) {
 #pragma unroll
-    for (int b = 0; b < 12; ++b) R.q[b] = F[b];
+    for (int b = 0; b < 12; ++b) rec[R_FI + LD * j + b] = F[b];
     double y[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int b = 0; b < 12; ++b) {
@@ -266,11 +266,16 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
     }
   }
   cta::bar();
-  // ---- (e) block-tridiagonal LDL' of the state system, one stage after the other (144 threads, entry per thread)
+  // ---- (e) TWISTED block LDL' of the state system (144 threads, one matrix entry per thread): stages 15..9 are
+  // eliminated upwards (U_s = Sig_s G_{s-1,s}' into T slot s-1), stages 0..7 downwards (T_s = Sig_s G_{s,s+1} into
+  // T slot s), stage 8 last with both Schur updates.  The solve then runs two chains of 7 steps at once.
   const int ei = tid / 12, ej = tid - 12 * ei;  // entry (ei, ej) for tid < 144
   const bool ent = tid < 144;
-  for (int s = 0; s < NS; ++s) {
-    double* G = S.Sig + MS * s;
+  for (int step = 0; step < NS; ++step) {
+    // order: 15, 14, ..., 9 (bottom), 0, 1, ..., 7 (top), 8 (middle)
+    const int sg = step < 7 ? NS - 1 - step : (step < 15 ? step - 7 : 8);
+    const bool bottom = step < 7;
+    double* G = S.Sig + MS * sg;
     // Gauss-Jordan inverse, ping-pong G <-> W (12 pivots: the result is back in G)
     for (int p = 0; p < 12; ++p) {
       const double* Wc = (p & 1) ? W : G;
@@ -289,23 +294,24 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
       }
       cta::bar();
     }
-    if (s == NS - 1) break;
-    double* O = S.T + MS * s;
-    // T_s = Sig_s G_{s,s+1}  (staged in W)
+    if (sg == 8) break;
+    const int so = bottom ? sg - 1 : sg;          // T slot holding the coupling block G_{so,so+1}
+    const int st = bottom ? sg - 1 : sg + 1;      // stage whose pivot block receives the Schur update
+    double* O = S.T + MS * so;
+    // coupling matrix Sig_s G' (bottom) or Sig_s G (top), staged in W
     if (ent) {
       double acc = 0.0;
 #pragma unroll
-      for (int m = 0; m < 12; ++m) acc += G[LD * ei + m] * O[LD * m + ej];
+      for (int m = 0; m < 12; ++m) acc += G[LD * ei + m] * (bottom ? O[LD * ej + m] : O[LD * m + ej]);
       W[12 * ei + ej] = acc;
     }
     cta::bar();
-    // G_{s+1,s+1} -= G_{s,s+1}' T_s ;  then the T slot takes T_s
     double tv = 0.0;
     if (ent) {
       double acc = 0.0;
 #pragma unroll
-      for (int m = 0; m < 12; ++m) acc += O[LD * m + ei] * W[12 * m + ej];
-      S.Sig[MS * (s + 1) + LD * ei + ej] -= acc;
+      for (int m = 0; m < 12; ++m) acc += (bottom ? O[LD * ei + m] : O[LD * m + ei]) * W[12 * m + ej];
+      S.Sig[MS * st + LD * ei + ej] -= acc;
       tv = W[12 * ei + ej];
     }
     cta::bar();
@@ -317,85 +323,105 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
 }
 
 // ------------------------------------------------------------------------------------------
-// State recurrences of one KKT solve, ONE warp, fully unrolled, 12-term dot products per lane:
-//   s_k   = A_k + CC_k                                             right-hand side of the state system
-//   s'_0  = s_0 ,  s'_{k+1} = s_{k+1} - T_k' s'_k                  forward   (lane i < 12; upper half mirrors)
-//   X_15  = Sig_15 s'_15 ,  X_k = Sig_k s'_k - T_k X_{k+1}         backward: lanes 16.. compute Sig_{k-1} s'_{k-1}
-//                                                                  one step ahead of the chain run by lanes 0..11
-// The vector of a step is broadcast through the record (STS, __syncwarp, LDS.128), not by shuffles.
+// State system of one KKT solve with the twisted factorisation, ONE warp, fully unrolled.  Lanes 0..11 run the
+// chain of stages 0..7 (downwards), lanes 16..27 the chain of stages 15..8 (upwards), in lockstep:
+//   s_k = A_k + CC_k
+//   elimination, 7 steps : s'_{k+1} = s_{k+1} - T_k' s'_k  |  s'_{k-1} = s_{k-1} - U_k' s'_k ;  v_k = Sig_k s'_k
+//   middle               : s''_8 = s'_8 - T_7' s'_7 ,  v_7 = Sig_7 s'_7 ,  X_8 = Sig_8 s''_8
+//   back-substitution    : X_k = v_k - T_k X_{k+1} (k = 7..0)  |  X_k = v_k - U_k X_{k-1} (k = 9..15)
+// T_k sits in T slot k (k <= 7), U_k in T slot k-1 (k >= 9).  The vector of a step is broadcast through the stage
+// record (STS, __syncwarp, LDS.128); v_k is parked in the A slot of its stage.
 // ------------------------------------------------------------------------------------------
-QRW_HD void state_recurrence(const Sm& S, int lane) {
+QRW_HD double dot12(const double* m, const double* v) {
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+  for (int jj = 8; jj >= 0; jj -= 4) {
+    a0 += m[jj] * v[jj];
+    a1 += m[jj + 1] * v[jj + 1];
+    a2 += m[jj + 2] * v[jj + 2];
+    a3 += m[jj + 3] * v[jj + 3];
+  }
+  return (a0 + a1) + (a2 + a3);
+}
+QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, int lane) {
   const int i0 = lane & 15;
   const bool up = lane >= 16;
   const int i = i0 < 12 ? i0 : 11;
-  const bool wr = lane < 12;
-  double* rec = S.rec;
-  double p = rec[R_A + i] + rec[R_CC + i];
-  if (wr) rec[R_SP + i] = p;
-#pragma unroll
-  for (int k = 0; k < NS - 1; ++k) {
-    const double* T = S.T + MS * k + i;
-    double* rn = rec + SR * (k + 1);
-    double tc[12];
-#pragma unroll
-    for (int jj = 0; jj < 12; ++jj) tc[jj] = T[LD * jj];
-    double a0 = rn[R_A + i] + rn[R_CC + i], a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    cta::wsync();
-    const double* pp = rec + SR * k + R_SP;
-    double pv[12];
-    cta::lds12(pp, pv);
-    cta::sched_fence();
-#pragma unroll
-    for (int jj = 8; jj >= 0; jj -= 4) {  // last-loaded elements first: every load is in flight before the first FMA
-      a0 -= tc[jj] * pv[jj];
-      a1 -= tc[jj + 1] * pv[jj + 1];
-      a2 -= tc[jj + 2] * pv[jj + 2];
-      a3 -= tc[jj + 3] * pv[jj + 3];
-    }
-    p = (a0 + a1) + (a2 + a3);
-    if (wr) rn[R_SP + i] = p;
-  }
-  cta::wsync();
-  // v_15 on every lane
-  double vcur;
+  const bool wr = i0 < 12;
+  // stage of this half at elimination step t: lower t, upper 15 - t
+  const int k0 = up ? NS - 1 : 0;
+  const int dk = up ? -1 : 1;
+  double p;
   {
-    const double* Sg = S.Sig + MS * (NS - 1) + LD * i;
-    const double* sp = rec + SR * (NS - 1) + R_SP;
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll
-    for (int jj = 0; jj < 12; jj += 4) {
-      a0 += Sg[jj] * sp[jj];
-      a1 += Sg[jj + 1] * sp[jj + 1];
-      a2 += Sg[jj + 2] * sp[jj + 2];
-      a3 += Sg[jj + 3] * sp[jj + 3];
-    }
-    vcur = (a0 + a1) + (a2 + a3);
+    double* r0 = rec + SR * k0;
+    p = r0[R_A + i] + r0[R_CC + i];
+    if (wr) r0[R_SP + i] = p;
   }
 #pragma unroll
-  for (int k = NS - 1; k >= 0; --k) {
-    // lower half: T_k X_{k+1} (nothing for k = 15); upper half: Sig_{k-1} s'_{k-1} (nothing for k = 0)
-    const int kt = (k < NS - 1) ? k : 0, ks = (k > 0) ? k - 1 : 0;
-    const double* mp = up ? (S.Sig + MS * ks + LD * i) : (S.T + MS * kt + LD * i);
-    const double* vp = up ? (rec + SR * ks + R_SP) : (rec + SR * (kt + 1) + R_XT);
-    double mr[12];
+  for (int t = 0; t < 7; ++t) {
+    const int kc = k0 + dk * t;       // stage whose s' is broadcast
+    const int kn = kc + dk;           // stage produced
+    const int slot = up ? kc - 1 : kc;
+    const double* Tc = Tm + MS * slot + i;  // column i of T_k / U_k
+    double* rc = rec + SR * kc;
+    double* rn = rec + SR * kn;
+    double tc[12], sg[12];
 #pragma unroll
-    for (int jj = 0; jj < 12; ++jj) mr[jj] = mp[jj];
-    if (k < NS - 1) cta::wsync();
-    double vv[12];
-    cta::lds12(vp, vv);
+    for (int jj = 0; jj < 12; ++jj) tc[jj] = Tc[LD * jj];
+    cta::lds12(Sig + MS * kc + LD * i, sg);
+    const double sn = rn[R_A + i] + rn[R_CC + i];
+    cta::wsync();
+    double pv[12];
+    cta::lds12(rc + R_SP, pv);
     cta::sched_fence();
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    p = sn - dot12(tc, pv);
+    if (wr) rn[R_SP + i] = p;
+    const double v = dot12(sg, pv);
+    if (wr) rc[R_A + i] = v;  // A_k was consumed one step ago
+  }
+  // ---- middle: every lane works on stages 7 / 8
+  cta::wsync();
+  double X;
+  {
+    double* r7 = rec + SR * 7;
+    double* r8 = rec + SR * 8;
+    double tc[12], sg[12], pv[12];
+    const double* Tc = Tm + MS * 7 + i;
 #pragma unroll
-    for (int jj = 8; jj >= 0; jj -= 4) {
-      a0 += mr[jj] * vv[jj];
-      a1 += mr[jj + 1] * vv[jj + 1];
-      a2 += mr[jj + 2] * vv[jj + 2];
-      a3 += mr[jj + 3] * vv[jj + 3];
+    for (int jj = 0; jj < 12; ++jj) tc[jj] = Tc[LD * jj];
+    cta::lds12(Sig + MS * 7 + LD * i, sg);
+    cta::lds12(r7 + R_SP, pv);
+    cta::sched_fence();
+    const double s8 = r8[R_SP + i] - dot12(tc, pv);
+    const double v7 = dot12(sg, pv);
+    cta::wsync();  // everybody has read s'_8 before it is replaced by s''_8
+    if (wr && !up) {
+      r8[R_SP + i] = s8;
+      r7[R_A + i] = v7;
     }
-    const double d = (a0 + a1) + (a2 + a3);
-    const double X = (k < NS - 1) ? vcur - d : vcur;
-    if (wr) rec[SR * k + R_XT + i] = X;
-    if (k > 0) vcur = cta::shfl_xor(d, 16);  // lanes 0..11 pick up v_{k-1} from lanes 16..27
+    cta::wsync();
+    cta::lds12(Sig + MS * 8 + LD * i, sg);
+    cta::lds12(r8 + R_SP, pv);
+    cta::sched_fence();
+    X = dot12(sg, pv);
+    if (wr && !up) r8[R_XT + i] = X;
+  }
+  // ---- back-substitution: lower half stages 7..0, upper half stages 9..15 (idle in the last step)
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int kk = up ? (u < 7 ? 9 + u : 15) : 7 - u;  // stage produced
+    const int kp = up ? kk - 1 : kk + 1;               // stage whose X is broadcast
+    const int slot = up ? kk - 1 : kk;
+    const double* Tr = Tm + MS * slot + LD * i;        // row i of T_k / U_k
+    double* rk = rec + SR * kk;
+    double tr[12], xv[12];
+    cta::lds12(Tr, tr);
+    const double vk = rk[R_A + i];
+    cta::wsync();
+    cta::lds12(rec + SR * kp + R_XT, xv);
+    cta::sched_fence();
+    X = vk - dot12(tr, xv);
+    if (wr && (!up || u < 7)) rk[R_XT + i] = X;
   }
 }
 
@@ -432,9 +458,8 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   if (tid < 32) gait[tid] = first ? 0 : st_i[tid];
   if (tid < NS) sb[tid] = first ? 0 : st_i[32 + tid];
 #pragma unroll
-  for (int t = 0; t < 15; ++t) R.q[t] = 0.0;
-#pragma unroll
   for (int t = 0; t < 6; ++t) R.gf[t] = 0.0;
+  R.bc[0] = R.bc[1] = R.bc[2] = 0.0;
   R.xf = R.xX = R.z1 = R.y1 = R.y2 = R.zA = R.yA = R.zB = R.yB = 0.0;
   if (!first && isv) {
     R.xf = st_d[ST_X + gvar(k, j)];
@@ -560,9 +585,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   }
   cta::bar();
   if (isv) {
-    R.q[12] = Bk[j];
-    R.q[13] = Bk[12 + j];
-    R.q[14] = Bk[24 + j];
+    R.bc[0] = Bk[j];
+    R.bc[1] = Bk[12 + j];
+    R.bc[2] = Bk[24 + j];
   }
   const int bit = isv ? ((sb[k] >> ft) & 1) : 0;
 
@@ -576,9 +601,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       const double d = R.dF;
       double nrm = cscale * C.wf * d * d;
       nrm = dmax(nrm, C.dtm * Ek[6 + c3] * d);
-      nrm = dmax(nrm, fabs(R.q[12]) * Ek[9] * d);
-      nrm = dmax(nrm, fabs(R.q[13]) * Ek[10] * d);
-      nrm = dmax(nrm, fabs(R.q[14]) * Ek[11] * d);
+      nrm = dmax(nrm, fabs(R.bc[0]) * Ek[9] * d);
+      nrm = dmax(nrm, fabs(R.bc[1]) * Ek[10] * d);
+      nrm = dmax(nrm, fabs(R.bc[2]) * Ek[11] * d);
       if (bit) nrm = dmax(nrm, e2 * d);
       const double* Ec = Ek + 24 + 5 * ft;
       if (c3 < 2) {
@@ -700,9 +725,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     // (2) t_f = sigma x_f + D_f (A' u)_f
     if (isv) {
       double v = C.dtm * BAk[6 + c3];
-      v += R.q[12] * BAk[9];
-      v += R.q[13] * BAk[10];
-      v += R.q[14] * BAk[11];
+      v += R.bc[0] * BAk[9];
+      v += R.bc[1] * BAk[10];
+      v += R.bc[2] * BAk[11];
       if (bit) v += u2;
       if (c3 < 2)
         v += uA - uB;
@@ -717,13 +742,14 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     if (isv) {
       double tv[12];
       cta::lds12(BBk, tv);
+      const double* fi = rec + R_FI + LD * j;
       double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
       for (int b = 0; b < 12; b += 4) {
-        a0 += R.q[b] * tv[b];
-        a1 += R.q[b + 1] * tv[b + 1];
-        a2 += R.q[b + 2] * tv[b + 2];
-        a3 += R.q[b + 3] * tv[b + 3];
+        a0 += fi[b] * tv[b];
+        a1 += fi[b + 1] * tv[b + 1];
+        a2 += fi[b + 2] * tv[b + 2];
+        a3 += fi[b + 3] * tv[b + 3];
       }
       uf = (a0 + a1) + (a2 + a3);
       if (j >= 6) {
@@ -750,49 +776,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
     }
     cta::bar();
-    if (w == recw) {
-      // park this warp's solver state in shared memory: the chain then has the registers to keep every load
-      // of a step in flight at once (with the state live ptxas serialised LDS -> DFMA -> LDS, r01 ncu)
-      double* sv = S.save + l;
-#pragma unroll
-      for (int t = 0; t < 15; ++t) sv[32 * t] = R.q[t];
-#pragma unroll
-      for (int t = 0; t < 6; ++t) sv[32 * (15 + t)] = R.gf[t];
-      sv[32 * 21] = R.xf;
-      sv[32 * 22] = R.xX;
-      sv[32 * 23] = R.z1;
-      sv[32 * 24] = R.y1;
-      sv[32 * 25] = R.y2;
-      sv[32 * 26] = R.zA;
-      sv[32 * 27] = R.yA;
-      sv[32 * 28] = R.zB;
-      sv[32 * 29] = R.yB;
-      sv[32 * 30] = uf;
-      sv[32 * 31] = wv;
-      state_recurrence(S, l);
-#pragma unroll
-      for (int t = 0; t < 15; ++t) R.q[t] = sv[32 * t];
-#pragma unroll
-      for (int t = 0; t < 6; ++t) R.gf[t] = sv[32 * (15 + t)];
-      R.xf = sv[32 * 21];
-      R.xX = sv[32 * 22];
-      R.z1 = sv[32 * 23];
-      R.y1 = sv[32 * 24];
-      R.y2 = sv[32 * 25];
-      R.zA = sv[32 * 26];
-      R.yA = sv[32 * 27];
-      R.zB = sv[32 * 28];
-      R.yB = sv[32 * 29];
-      uf = sv[32 * 30];
-      wv = sv[32 * 31];
-      if (isv) {
-        R.dF = Dk[j];
-        R.dX = Dk[12 + j];
-        R.e1 = Ek[j];
-        R.eA = Ek[rowA];
-        if (hasB) R.eB = Ek[rowA + 1];
-      }
-    }
+    // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
+    // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
+    if (w == recw) state_recurrence(S.Sig, S.T, S.rec, l);
     cta::bar();
     // (5) dynamics rows applied to the new states: r = E (-D_X x~_X + A D_X x~_X^{k-1})
     double xtX = 0.0, rX = 0.0;
@@ -904,9 +890,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         // force variable
         const double* u = rec + R_A;
         double v = C.dtm * u[6 + c3];
-        v += R.q[12] * u[9];
-        v += R.q[13] * u[10];
-        v += R.q[14] * u[11];
+        v += R.bc[0] * u[9];
+        v += R.bc[1] * u[10];
+        v += R.bc[2] * u[11];
         if (bit) v += BBk[j];
         if (c3 < 2)
           v += yA - yB;
