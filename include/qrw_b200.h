@@ -31,6 +31,7 @@ extern "C" {
 
 typedef struct qrw_mpc qrw_mpc_t;
 typedef struct qrw_wbc qrw_wbc_t;
+typedef struct qrw_wbctick qrw_wbctick_t;
 
 const char* qrw_last_error(void);
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
@@ -109,6 +110,34 @@ int qrw_invkin_run_device(int batch, const double* contacts, const double* goals
 int qrw_invkin_run_host(int batch, const double* contacts, const double* goals, const double* vgoals,
                         const double* agoals, const double* posf, const double* vf, const double* wf,
                         const double* af, const double* Jf, double* ddq, double* dq_cmd, double* q_step);
+
+/* ---------------------------------------------------------------------------------------
+ * Whole-body tick -- replaces wbc_controller.compute (scripts/QP_WBC.py:52-131) for B robots: the Pinocchio
+ * calls around the C++ classes (fixed-base foot kinematics solo12InvKin.py:47-59, contact Jacobians
+ * QP_WBC.py:96-101, rnea :104,:116, constant crba diagonal :89-93), InvKin::refreshAndCompute, QPWBC::run and
+ * tau_ff = rnea(q, dq, ddq_cmd + [ddq_res; 0])[6:] - Jc[:, 6:]' f_res (:110-117).
+ * q [B][19] (xyz, quaternion xyzw, 12 joints), dq [B][18] (base twist in the base frame, 12 joints),
+ * f_cmd [B][12], contacts [B][4], pgoals / vgoals / agoals [B][12] (3 x 4 column-major);
+ * outputs [B][12]: tau_ff, qdes (joints: q + q_step), vdes (dq_cmd), f_res (f_with_delta), ddq_cmd (joints).
+ * Solo12 constants: include/solo12_model.h (not in the reference tree: PARITY UNPINNED at this sub-boundary).
+ * ------------------------------------------------------------------------------------- */
+int qrw_wbctick_create(qrw_wbctick_t** out, int batch, int device);
+int qrw_wbctick_destroy(qrw_wbctick_t* h);
+int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd,
+                           const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                           void* stream);
+int qrw_wbctick_run_host(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, const double* contacts,
+                         const double* pgoals, const double* vgoals, const double* agoals);
+int qrw_wbctick_result_host(qrw_wbctick_t* h, double* tau_ff, double* qdes, double* vdes, double* f_res, double* ddq_cmd);
+int qrw_wbctick_result_device(qrw_wbctick_t* h, const double** tau_ff, const double** qdes, const double** vdes,
+                              const double** f_res);
+/* intermediates handed to QPWBC (Jc [B][216], RNEA [B][6]) and its ddq_res [B][6]; any pointer may be NULL */
+int qrw_wbctick_debug_host(qrw_wbctick_t* h, double* Jc, double* rnea6, double* ddq_res);
+/* diag(crba(q = 0)[:6, :6]): (m, m, m, Ixx, Iyy, Izz) of the whole robot about the base frame */
+int qrw_solo12_base_inertia(double* Y6);
+/* what solo12InvKin.py:47-59 reads from Pinocchio: q12, dq12 [B][12] -> posf, vf, wf, af [B][4*3], Jf [B][12*12] */
+int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, double* posf, double* vf, double* wf,
+                         double* af, double* Jf);
 
 #ifdef __cplusplus
 }

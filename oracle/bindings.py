@@ -63,6 +63,10 @@ def lib():
         L.orc_pinv6.argtypes = [_dp, _dp]
         L.orc_invkin_run.argtypes = [C.c_int] + [_dp] * 12
         L.orc_osqp_dense.argtypes = [C.c_int, C.c_int] + [_dp] * 5 + [C.c_double, C.c_int, _dp, _dp, _ip]
+        L.orc_solo12_feet.argtypes = [C.c_int] + [_dp] * 7
+        L.orc_solo12_rnea.argtypes = [C.c_int] + [_dp] * 4
+        L.orc_solo12_jc.argtypes = [C.c_int] + [_dp] * 3
+        L.orc_solo12_crba.argtypes = [_dp, _dp]
         _lib = L
     return _lib
 
@@ -213,6 +217,67 @@ def osqp_dense(P, A, q, l, u, eps=1e-8, max_iter=20000):
     it = np.zeros(1, np.int32)
     st = lib().orc_osqp_dense(n, m, _d(P), _d(A), _d(q), _d(l), _d(u), float(eps), int(max_iter), _d(x), _d(y), _i(it))
     return x, y, int(it[0]), st
+
+
+# ---------------------------------------------------------------------------------------------
+# Solo12 rigid-body quantities (what the reference gets from Pinocchio; oracle/solo12_oracle.cpp)
+# ---------------------------------------------------------------------------------------------
+def solo12_feet(q12, dq12):
+    """solo12InvKin.py:47-59: (posf, vf, wf, af [B,12] as 4x3 column-major, Jf [B,144] as 12x12 column-major)."""
+    q12, dq12 = _c(q12), _c(dq12)
+    B = q12.size // 12
+    outs = [np.empty((B, 12)) for _ in range(4)] + [np.empty((B, 144))]
+    lib().orc_solo12_feet(B, _d(q12), _d(dq12), *[_d(o) for o in outs])
+    return outs
+
+
+def solo12_rnea(q, v, a):
+    q, v, a = _c(q), _c(v), _c(a)
+    B = q.size // 19
+    tau = np.empty((B, 18))
+    lib().orc_solo12_rnea(B, _d(q), _d(v), _d(a), _d(tau))
+    return tau
+
+
+def solo12_jc(q, contacts):
+    q, contacts = _c(q), _c(contacts)
+    B = q.size // 19
+    Jc = np.empty((B, 216))
+    lib().orc_solo12_jc(B, _d(q), _d(contacts), _d(Jc))
+    return Jc
+
+
+def solo12_crba(q):
+    q = _c(q)
+    M = np.empty((18, 18), order="F")
+    lib().orc_solo12_crba(_d(q), _d(M))
+    return M
+
+
+def wbc_tick(owbc, q, dq, f_cmd, contacts, pgoals, vgoals, agoals, nthreads=1):
+    """wbc_controller.compute (scripts/QP_WBC.py:52-131) for a batch, composed from the oracle's pieces.
+    owbc: OracleWBC carrying the QP's warm start.  Returns dict(tau_ff, qdes, vdes, f_res, ddq_cmd, Jc, RNEA, ddq_res)."""
+    q, dq = _c(q).reshape(-1, 19), _c(dq).reshape(-1, 18)
+    B = q.shape[0]
+    posf, vf, wf, af, Jf = solo12_feet(q[:, 7:], dq[:, 6:])
+    ddq, dq_cmd, q_step = invkin(contacts, pgoals, vgoals, agoals, posf, vf, wf, af, Jf)
+    q0 = np.zeros(19)
+    q0[6] = 1.0
+    M = solo12_crba(q0)
+    M[:6, :6] = M[:6, :6] * np.eye(6)  # QP_WBC.py:93
+    Mb = np.tile(np.asfortranarray(M).ravel(order="F"), (B, 1))
+    Jc = solo12_jc(q, contacts)
+    acc = np.zeros((B, 18))
+    acc[:, 6:] = ddq
+    RNEA = solo12_rnea(q, dq, acc)[:, :6]
+    owbc.run(Mb, Jc, f_cmd, RNEA, nthreads)
+    f_res, ddq_res, _ = owbc.results()
+    acc[:, :6] += ddq_res
+    tau = solo12_rnea(q, dq, acc)[:, 6:]
+    Jm = Jc.reshape(B, 18, 12).transpose(0, 2, 1)  # [B, 12, 18]
+    tau_ff = tau - np.einsum("bij,bi->bj", Jm[:, :, 6:], f_res)
+    return dict(tau_ff=tau_ff, qdes=q[:, 7:] + q_step, vdes=dq_cmd, f_res=f_res, ddq_cmd=ddq, Jc=Jc, RNEA=RNEA,
+                ddq_res=ddq_res)
 
 
 # ---------------------------------------------------------------------------------------------

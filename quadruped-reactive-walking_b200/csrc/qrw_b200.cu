@@ -20,6 +20,7 @@
 #include "mpc_cta_core.cuh"
 #include "mpc_v2_core.cuh"
 #include "wbc_core.cuh"
+#include "solo12_core.cuh"
 
 using namespace qrw;
 
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(32 * WBC_WARPS) wbc_solve_kernel(const WbcCons
                                                                   const double* __restrict__ f_cmd,
                                                                   const double* __restrict__ RNEA, double* st,
                                                                   double* f_res, double* ddq_res, double* H,
-                                                                  int* info, int* counter) {
+                                                                  int* info, int* counter, const int m_stride) {
   extern __shared__ __align__(16) double slab[];
   double* sl = slab + (threadIdx.x >> 5) * WBC_SLAB_DOUBLES;
   const int lane = threadIdx.x & 31;
@@ -140,7 +141,7 @@ __global__ void __launch_bounds__(32 * WBC_WARPS) wbc_solve_kernel(const WbcCons
     if (lane == 0) b = atomicAdd(counter, 1);
     b = __shfl_sync(0xffffffffu, b, 0);
     if (b >= B) break;
-    wbc_solve_instance(C, sl, M + (size_t)b * 324, Jc + (size_t)b * 216, f_cmd + (size_t)b * 12,
+    wbc_solve_instance(C, sl, M + (size_t)b * m_stride, Jc + (size_t)b * 216, f_cmd + (size_t)b * 12,
                        RNEA + (size_t)b * 6, st + (size_t)b * WBC_STATE_DOUBLES, first, f_res + (size_t)b * 12,
                        ddq_res + (size_t)b * 6, H ? H + (size_t)b * 144 : nullptr, info + 4 * b);
     __syncwarp();
@@ -204,6 +205,174 @@ __global__ void __launch_bounds__(128) invkin_kernel(const int B, const double* 
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Whole-body tick around the QPWBC solve (scripts/QP_WBC.py:52-131), four threads per robot (one per leg).
+//   pre : fixed-base leg kinematics (solo12InvKin.py:47-59) -> InvKin (src/InvKin.cpp:23-73) -> contact Jacobians
+//         (QP_WBC.py:96-101) and the base wrench of rnea(q, dq, ddq_cmd) (:104)
+//   post: rnea(q, dq, ddq_cmd + [ddq_res; 0])[6:] - Jc[:, 6:]' f_res (:110-117)
+// Layouts: q [B][19] (xyz, quaternion xyzw, 12 joints), dq [B][18] (base linear and angular velocity in the base
+// frame, 12 joints), contacts [B][4], goals [B][12] (3 x 4 column-major), Jc [B][12*18] column-major.
+// ------------------------------------------------------------------------------------------
+struct BaseState {
+  s12::M3 R;
+  s12::V3 vb, wb;
+};
+__device__ __forceinline__ BaseState load_base(const double* q, const double* dq) {
+  BaseState S;
+  S.R = s12::quat_to_rot(q[3], q[4], q[5], q[6]);
+  S.vb = s12::v3(dq[0], dq[1], dq[2]);
+  S.wb = s12::v3(dq[3], dq[4], dq[5]);
+  return S;
+}
+__global__ void __launch_bounds__(128) wbc_tick_pre_kernel(const int B, const double* __restrict__ q,
+                                                           const double* __restrict__ dq,
+                                                           const double* __restrict__ contacts,
+                                                           const double* __restrict__ pgoals,
+                                                           const double* __restrict__ vgoals,
+                                                           const double* __restrict__ agoals, double* Jc,
+                                                           double* rnea6, double* ddq_cmd, double* vdes,
+                                                           double* qdes) {
+  using namespace s12;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int leg = t & 3;
+  const bool valid = (t >> 2) < B;
+  const size_t b = valid ? (size_t)(t >> 2) : (size_t)(B - 1);
+  const double* qb = q + b * 19;
+  const double* dqb = dq + b * 18;
+  double qj[3], dqj[3];
+  for (int c = 0; c < 3; ++c) {
+    qj[c] = qb[7 + 3 * leg + c];
+    dqj[c] = dqb[6 + 3 * leg + c];
+  }
+  const LegKin K = leg_kinematics(leg, qj);
+  V3 J[3], Ji[3];
+  leg_jacobian(K, J);
+  V3 vf, wf, acl;
+  foot_motion(K, dqj, vf, wf, acl);
+  // InvKin::refreshAndCompute for this foot (Kp = 100, Kd = 20, src/InvKin.hpp:56-57)
+  const double* pg = pgoals + b * 12 + 3 * leg;
+  const double* vgp = vgoals + b * 12 + 3 * leg;
+  const double* agp = agoals + b * 12 + 3 * leg;
+  const V3 e = v3(pg[0], pg[1], pg[2]) - K.pf;
+  const V3 vg = v3(vgp[0], vgp[1], vgp[2]);
+  V3 a = 100.0 * e - 20.0 * (vf - vg) + v3(agp[0], agp[1], agp[2]);
+  const bool contact = contacts[b * 4 + leg] != 0.0;
+  if (contact) a = 0.0 * a;
+  a = a - acl;  // af + wf x vf of InvKin.cpp:48 = classical acceleration of the foot point
+  inv3(J, Ji);
+  const V3 dd = a.x * Ji[0] + (a.y * Ji[1] + a.z * Ji[2]);
+  const V3 dv = vg.x * Ji[0] + (vg.y * Ji[1] + vg.z * Ji[2]);
+  const V3 qs = e.x * Ji[0] + (e.y * Ji[1] + e.z * Ji[2]);
+  const double ddq[3] = {dd.x, dd.y, dd.z};
+  // rnea(q, dq, [0; ddq_cmd]): base wrench
+  const BaseState S = load_base(qb, dqb);
+  const V3 ab = cross(S.wb, S.vb) + S12_GRAVITY * v3(S.R.c0.z, S.R.c1.z, S.R.c2.z);  // R' (0, 0, g)
+  const LegDyn D = leg_dynamics(leg, K, S.wb, v3(0.0, 0.0, 0.0), ab, dqj, ddq);
+  double w6[6] = {D.f.x, D.f.y, D.f.z, D.n.x, D.n.y, D.n.z};
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    w6[c] += __shfl_xor_sync(0xffffffffu, w6[c], 1);
+    w6[c] += __shfl_xor_sync(0xffffffffu, w6[c], 2);
+  }
+  if (!valid) return;
+  if (leg == 0) {
+    V3 fb, nb;
+    base_dynamics(S.wb, v3(0.0, 0.0, 0.0), ab, fb, nb);
+    double* r = rnea6 + b * 6;
+    r[0] = w6[0] + fb.x;
+    r[1] = w6[1] + fb.y;
+    r[2] = w6[2] + fb.z;
+    r[3] = w6[3] + nb.x;
+    r[4] = w6[4] + nb.y;
+    r[5] = w6[5] + nb.z;
+  }
+  for (int c = 0; c < 3; ++c) {
+    ddq_cmd[b * 12 + 3 * leg + c] = ddq[c];
+    vdes[b * 12 + 3 * leg + c] = c == 0 ? dv.x : (c == 1 ? dv.y : dv.z);
+    qdes[b * 12 + 3 * leg + c] = qj[c] + (c == 0 ? qs.x : (c == 1 ? qs.y : qs.z));
+  }
+  // contact Jacobian rows of this foot (LOCAL_WORLD_ALIGNED, linear part): [R | R (e_c x pf) | R J_leg], zero if swinging
+  double* Jr = Jc + b * 216 + 3 * leg;
+  const double on = contact ? 1.0 : 0.0;
+  for (int c = 0; c < 18; ++c) {
+    V3 col = v3(0.0, 0.0, 0.0);
+    if (c < 3)
+      col = c == 0 ? S.R.c0 : (c == 1 ? S.R.c1 : S.R.c2);
+    else if (c < 6) {
+      const V3 ec = v3(c == 3 ? 1.0 : 0.0, c == 4 ? 1.0 : 0.0, c == 5 ? 1.0 : 0.0);
+      col = mul(S.R, cross(ec, K.pf));
+    } else if (c >= 6 + 3 * leg && c < 9 + 3 * leg)
+      col = mul(S.R, J[c - 6 - 3 * leg]);
+    Jr[12 * c] = on * col.x;
+    Jr[12 * c + 1] = on * col.y;
+    Jr[12 * c + 2] = on * col.z;
+  }
+}
+__global__ void __launch_bounds__(128) wbc_tick_post_kernel(const int B, const double* __restrict__ q,
+                                                            const double* __restrict__ dq,
+                                                            const double* __restrict__ contacts,
+                                                            const double* __restrict__ ddq_cmd,
+                                                            const double* __restrict__ ddq_res,
+                                                            const double* __restrict__ f_res, double* tau_ff) {
+  using namespace s12;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int leg = t & 3;
+  if ((t >> 2) >= B) return;
+  const size_t b = (size_t)(t >> 2);
+  const double* qb = q + b * 19;
+  const double* dqb = dq + b * 18;
+  double qj[3], dqj[3], ddq[3];
+  for (int c = 0; c < 3; ++c) {
+    qj[c] = qb[7 + 3 * leg + c];
+    dqj[c] = dqb[6 + 3 * leg + c];
+    ddq[c] = ddq_cmd[b * 12 + 3 * leg + c];
+  }
+  const LegKin K = leg_kinematics(leg, qj);
+  V3 J[3];
+  leg_jacobian(K, J);
+  const BaseState S = load_base(qb, dqb);
+  const double* dr = ddq_res + b * 6;
+  const V3 ab = v3(dr[0], dr[1], dr[2]) + cross(S.wb, S.vb) + S12_GRAVITY * v3(S.R.c0.z, S.R.c1.z, S.R.c2.z);
+  const LegDyn D = leg_dynamics(leg, K, S.wb, v3(dr[3], dr[4], dr[5]), ab, dqj, ddq);
+  const double* fr = f_res + b * 12 + 3 * leg;
+  const V3 fl = (contacts[b * 4 + leg] != 0.0) ? mulT(S.R, v3(fr[0], fr[1], fr[2])) : v3(0.0, 0.0, 0.0);  // R' f
+  for (int c = 0; c < 3; ++c) tau_ff[b * 12 + 3 * leg + c] = D.tau[c] - dot(J[c], fl);
+}
+// the Pinocchio sub-boundary of scripts/solo12InvKin.py:47-59 on its own (parity tests, drop-in Solo12InvKin):
+// posf, vf, wf, af [B][4*3] column-major 4 x 3, Jf [B][12*12] column-major
+__global__ void __launch_bounds__(128) solo12_feet_kernel(const int B, const double* __restrict__ q12,
+                                                          const double* __restrict__ dq12, double* posf, double* vf,
+                                                          double* wf, double* af, double* Jf) {
+  using namespace s12;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int leg = t & 3;
+  if ((t >> 2) >= B) return;
+  const size_t b = (size_t)(t >> 2);
+  double qj[3], dqj[3];
+  for (int c = 0; c < 3; ++c) {
+    qj[c] = q12[b * 12 + 3 * leg + c];
+    dqj[c] = dq12[b * 12 + 3 * leg + c];
+  }
+  const LegKin K = leg_kinematics(leg, qj);
+  V3 J[3], v, w, acl;
+  leg_jacobian(K, J);
+  foot_motion(K, dqj, v, w, acl);
+  const V3 asp = acl - cross(w, v);  // spatial acceleration, what getFrameAcceleration returns
+  const size_t o = b * 12 + leg;
+  posf[o] = K.pf.x, posf[o + 4] = K.pf.y, posf[o + 8] = K.pf.z;
+  vf[o] = v.x, vf[o + 4] = v.y, vf[o + 8] = v.z;
+  wf[o] = w.x, wf[o + 4] = w.y, wf[o + 8] = w.z;
+  af[o] = asp.x, af[o + 4] = asp.y, af[o + 8] = asp.z;
+  double* Jb = Jf + b * 144;
+  for (int c = 0; c < 12; ++c) {
+    const bool mine = c >= 3 * leg && c < 3 * leg + 3;
+    const V3 col = mine ? J[c - 3 * leg] : v3(0.0, 0.0, 0.0);
+    Jb[3 * leg + 12 * c] = col.x;
+    Jb[3 * leg + 1 + 12 * c] = col.y;
+    Jb[3 * leg + 2 + 12 * c] = col.z;
+  }
+}
+
 // FP64 FMA peak: 8 independent DFMA chains per thread, 1024 threads per SM-slot
 __global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double a, double b) {
   double v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3, v4 = v0 + 4, v5 = v0 + 5, v6 = v0 + 6, v7 = v0 + 7;
@@ -246,11 +415,46 @@ struct qrw_wbc {
   int B, device, sms;
   WbcConst C;
   bool first = true;
+  int m_stride = 324;  // 0: one M shared by the whole batch (the fused whole-body tick, where M is a model constant)
   double *d_M = nullptr, *d_Jc = nullptr, *d_f = nullptr, *d_R = nullptr, *d_state = nullptr, *d_fres = nullptr,
          *d_ddq = nullptr, *d_H = nullptr;
   int *d_info = nullptr, *d_counter = nullptr;
   cudaStream_t stream = nullptr;
 };
+
+// whole-body tick: QPWBC handle + the buffers between its three kernels
+struct qrw_wbctick {
+  int B, device;
+  qrw_wbc* wbc = nullptr;
+  double *d_q = nullptr, *d_dq = nullptr, *d_f = nullptr, *d_c = nullptr, *d_pg = nullptr, *d_vg = nullptr,
+         *d_ag = nullptr;                                                      // staging of the host entry point
+  double *d_Jc = nullptr, *d_rnea = nullptr, *d_ddq = nullptr, *d_vdes = nullptr, *d_qdes = nullptr, *d_tau = nullptr;
+};
+
+// diag of crba(q = 0)[:6, :6] (scripts/QP_WBC.py:89-93): total mass, and the moments of inertia of the whole robot
+// about the axes of the base frame at the zero configuration
+static void solo12_base_inertia(double Y[6]) {
+  double m = S12_BASE_MASS, I[3] = {S12_BASE_IXX, S12_BASE_IYY, S12_BASE_IZZ};
+  for (int leg = 0; leg < 4; ++leg) {
+    const double sx = leg < 2 ? 1.0 : -1.0, sy = (leg & 1) ? -1.0 : 1.0;
+    const double o0[3] = {sx * S12_HAA_X, sy * S12_HAA_Y, 0.0};
+    const double o1[3] = {o0[0], o0[1] + sy * S12_HFE_Y, o0[2]};
+    const double o2[3] = {o1[0], o1[1] + sy * S12_KFE_Y, o1[2] + S12_KFE_Z};
+    const double mass[3] = {S12_L0_MASS, S12_L1_MASS, S12_L2_MASS};
+    const double com[3][3] = {{o0[0] + sx * S12_L0_CX, o0[1] + sy * S12_L0_CY, o0[2] + S12_L0_CZ},
+                              {o1[0] + S12_L1_CX, o1[1] + sy * S12_L1_CY, o1[2] + S12_L1_CZ},
+                              {o2[0] + S12_L2_CX, o2[1] + sy * S12_L2_CY, o2[2] + S12_L2_CZ}};
+    const double Id[3][3] = {{S12_L0_IXX, S12_L0_IYY, S12_L0_IZZ}, {S12_L1_IXX, S12_L1_IYY, S12_L1_IZZ},
+                             {S12_L2_IXX, S12_L2_IYY, S12_L2_IZZ}};
+    for (int l = 0; l < 3; ++l) {
+      m += mass[l];
+      const double r2 = com[l][0] * com[l][0] + com[l][1] * com[l][1] + com[l][2] * com[l][2];
+      for (int a = 0; a < 3; ++a) I[a] += Id[l][a] + mass[l] * (r2 - com[l][a] * com[l][a]);
+    }
+  }
+  Y[0] = Y[1] = Y[2] = m;
+  Y[3] = I[0], Y[4] = I[1], Y[5] = I[2];
+}
 
 extern "C" {
 
@@ -579,7 +783,7 @@ int qrw_wbc_run_device(qrw_wbc_t* h, const double* d_M, const double* d_Jc, cons
   if (grid > need) grid = need;
   wbc_solve_kernel<<<grid, 32 * WBC_WARPS, WBC_WARPS * WBC_SLAB_BYTES, s>>>(
       h->C, h->B, h->first ? 1 : 0, d_M, d_Jc, d_f_cmd, d_RNEA, h->d_state, h->d_fres, h->d_ddq, h->d_H, h->d_info,
-      h->d_counter);
+      h->d_counter, h->m_stride);
   ++g_launches;
   CU(cudaGetLastError());
   h->first = false;  // QPWBC::initialized, src/QPWBC.cpp:23,254
@@ -678,6 +882,138 @@ int qrw_invkin_run_host(int batch, const double* contacts, const double* goals, 
   for (int i = 0; i < 9; ++i) cudaFree(in_d[i]);
   for (int i = 0; i < 3; ++i) cudaFree(out_d[i]);
   return rc;
+}
+
+// ---------------------------------------------------------------- whole-body tick (QP_WBC.py:52-131)
+int qrw_wbctick_create(qrw_wbctick_t** out, int batch, int device) {
+  if (!out) return fail("qrw_wbctick_create: null output handle");
+  qrw_wbc_t* w = nullptr;
+  if (qrw_wbc_create(&w, batch, device)) return 1;
+  auto* h = new qrw_wbctick();
+  h->B = batch;
+  h->device = device;
+  h->wbc = w;
+  const size_t B = (size_t)batch;
+  w->m_stride = 0;  // M is a model constant here: one copy for the whole batch
+  double M[324] = {0.0}, Y[6];
+  solo12_base_inertia(Y);
+  for (int i = 0; i < 6; ++i) M[i + 18 * i] = Y[i];
+  CU(cudaMemcpy(w->d_M, M, sizeof(M), cudaMemcpyHostToDevice));
+  const size_t sz[13] = {19, 18, 12, 4, 12, 12, 12, 216, 6, 12, 12, 12, 12};
+  double** p[13] = {&h->d_q, &h->d_dq, &h->d_f, &h->d_c, &h->d_pg, &h->d_vg, &h->d_ag, &h->d_Jc, &h->d_rnea, &h->d_ddq,
+                    &h->d_vdes, &h->d_qdes, &h->d_tau};
+  for (int i = 0; i < 13; ++i) {
+    CU(cudaMalloc(p[i], B * sz[i] * sizeof(double)));
+    CU(cudaMemset(*p[i], 0, B * sz[i] * sizeof(double)));
+  }
+  *out = h;
+  return 0;
+}
+int qrw_wbctick_destroy(qrw_wbctick_t* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  double* p[13] = {h->d_q, h->d_dq, h->d_f, h->d_c, h->d_pg, h->d_vg, h->d_ag, h->d_Jc, h->d_rnea, h->d_ddq, h->d_vdes,
+                   h->d_qdes, h->d_tau};
+  for (double* x : p) cudaFree(x);
+  qrw_wbc_destroy(h->wbc);
+  delete h;
+  return 0;
+}
+int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd,
+                           const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                           void* stream) {
+  if (!h || !q || !dq || !f_cmd || !contacts || !pgoals || !vgoals || !agoals)
+    return fail("qrw_wbctick_run_device: null argument");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)((4LL * h->B + 127) / 128);
+  wbc_tick_pre_kernel<<<grid, 128, 0, s>>>(h->B, q, dq, contacts, pgoals, vgoals, agoals, h->d_Jc, h->d_rnea, h->d_ddq,
+                                           h->d_vdes, h->d_qdes);
+  ++g_launches;
+  CU(cudaGetLastError());
+  if (qrw_wbc_run_device(h->wbc, h->wbc->d_M, h->d_Jc, f_cmd, h->d_rnea, s)) return 1;
+  wbc_tick_post_kernel<<<grid, 128, 0, s>>>(h->B, q, dq, contacts, h->d_ddq, h->wbc->d_ddq, h->wbc->d_fres, h->d_tau);
+  ++g_launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+int qrw_wbctick_run_host(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, const double* contacts,
+                         const double* pgoals, const double* vgoals, const double* agoals) {
+  if (!h || !q || !dq || !f_cmd || !contacts || !pgoals || !vgoals || !agoals)
+    return fail("qrw_wbctick_run_host: null argument");
+  CU(cudaSetDevice(h->device));
+  const size_t B = (size_t)h->B;
+  cudaStream_t s = h->wbc->stream;
+  const size_t sz[7] = {19, 18, 12, 4, 12, 12, 12};
+  const double* src[7] = {q, dq, f_cmd, contacts, pgoals, vgoals, agoals};
+  double* dst[7] = {h->d_q, h->d_dq, h->d_f, h->d_c, h->d_pg, h->d_vg, h->d_ag};
+  for (int i = 0; i < 7; ++i) CU(cudaMemcpyAsync(dst[i], src[i], B * sz[i] * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (qrw_wbctick_run_device(h, h->d_q, h->d_dq, h->d_f, h->d_c, h->d_pg, h->d_vg, h->d_ag, s)) return 1;
+  CU(cudaStreamSynchronize(s));
+  return 0;
+}
+int qrw_wbctick_result_host(qrw_wbctick_t* h, double* tau_ff, double* qdes, double* vdes, double* f_res, double* ddq_cmd) {
+  if (!h) return fail("qrw_wbctick_result_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  const size_t n = (size_t)h->B * 12 * sizeof(double);
+  if (tau_ff) CU(cudaMemcpy(tau_ff, h->d_tau, n, cudaMemcpyDeviceToHost));
+  if (qdes) CU(cudaMemcpy(qdes, h->d_qdes, n, cudaMemcpyDeviceToHost));
+  if (vdes) CU(cudaMemcpy(vdes, h->d_vdes, n, cudaMemcpyDeviceToHost));
+  if (f_res) CU(cudaMemcpy(f_res, h->wbc->d_fres, n, cudaMemcpyDeviceToHost));
+  if (ddq_cmd) CU(cudaMemcpy(ddq_cmd, h->d_ddq, n, cudaMemcpyDeviceToHost));
+  return 0;
+}
+int qrw_wbctick_result_device(qrw_wbctick_t* h, const double** tau_ff, const double** qdes, const double** vdes,
+                              const double** f_res) {
+  if (!h) return fail("qrw_wbctick_result_device: null handle");
+  if (tau_ff) *tau_ff = h->d_tau;
+  if (qdes) *qdes = h->d_qdes;
+  if (vdes) *vdes = h->d_vdes;
+  if (f_res) *f_res = h->wbc->d_fres;
+  return 0;
+}
+int qrw_wbctick_debug_host(qrw_wbctick_t* h, double* Jc, double* rnea6, double* ddq_res) {
+  if (!h) return fail("qrw_wbctick_debug_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  const size_t B = (size_t)h->B;
+  if (Jc) CU(cudaMemcpy(Jc, h->d_Jc, B * 216 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (rnea6) CU(cudaMemcpy(rnea6, h->d_rnea, B * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (ddq_res) CU(cudaMemcpy(ddq_res, h->wbc->d_ddq, B * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+int qrw_solo12_base_inertia(double* Y6) {
+  if (!Y6) return fail("qrw_solo12_base_inertia: null argument");
+  solo12_base_inertia(Y6);
+  return 0;
+}
+// Fixed-base foot kinematics (scripts/solo12InvKin.py:47-59): q12, dq12 [B][12] -> posf, vf, wf, af [B][12]
+// (4 x 3 column-major), Jf [B][144] (12 x 12 column-major).  Host pointers.
+int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, double* posf, double* vf, double* wf,
+                         double* af, double* Jf) {
+  if (batch <= 0 || !q12 || !dq12 || !posf || !vf || !wf || !af || !Jf) return fail("qrw_solo12_feet_host: bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail("qrw_solo12_feet_host: no CUDA device (this library has no CPU fallback)");
+  const size_t B = (size_t)batch;
+  double* d = nullptr;
+  CU(cudaMalloc(&d, B * (12 + 12 + 48 + 144) * sizeof(double)));
+  double *dq_ = d + B * 12, *dp = d + B * 24, *dv = dp + B * 12, *dw = dv + B * 12, *da = dw + B * 12, *dJ = da + B * 12;
+  cudaError_t e = cudaMemcpy(d, q12, B * 12 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(dq_, dq12, B * 12 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    solo12_feet_kernel<<<(unsigned)((4 * B + 127) / 128), 128>>>(batch, d, dq_, dp, dv, dw, da, dJ);
+    ++g_launches;
+    e = cudaGetLastError();
+  }
+  double* outs[4] = {posf, vf, wf, af};
+  double* srcs[4] = {dp, dv, dw, da};
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaMemcpy(outs[i], srcs[i], B * 12 * sizeof(double), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(Jf, dJ, B * 144 * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(std::string("qrw_solo12_feet_host: ") + cudaGetErrorString(e));
+  return 0;
 }
 
 }  // extern "C"

@@ -6,4 +6,4 @@ no CPU fallback: constructing any solver without the built library or without a 
 raises ``QrwError``.
 """
 from ._lib import QrwError, build_library, library_path, load_library  # noqa: F401
-from .batched import BatchedInvKin, BatchedMPC, BatchedQPWBC  # noqa: F401
+from .batched import BatchedInvKin, BatchedMPC, BatchedQPWBC, BatchedWbcTick, solo12_base_inertia, solo12_feet  # noqa: F401

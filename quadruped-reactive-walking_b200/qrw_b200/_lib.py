@@ -73,6 +73,15 @@ _SIGNATURES = {
     "qrw_wbc_info_host": (C.c_int, [_vp, _vp, _vp, _vp]),
     "qrw_invkin_run_device": (C.c_int, [C.c_int] + [_vp] * 13),
     "qrw_invkin_run_host": (C.c_int, [C.c_int] + [_vp] * 12),
+    "qrw_wbctick_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int]),
+    "qrw_wbctick_destroy": (C.c_int, [_vp]),
+    "qrw_wbctick_run_device": (C.c_int, [_vp] * 9),
+    "qrw_wbctick_run_host": (C.c_int, [_vp] * 8),
+    "qrw_wbctick_result_host": (C.c_int, [_vp] * 6),
+    "qrw_wbctick_result_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 4),
+    "qrw_wbctick_debug_host": (C.c_int, [_vp] * 4),
+    "qrw_solo12_base_inertia": (C.c_int, [_vp]),
+    "qrw_solo12_feet_host": (C.c_int, [C.c_int] + [_vp] * 7),
 }
 
 

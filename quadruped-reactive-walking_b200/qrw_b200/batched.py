@@ -247,3 +247,70 @@ class BatchedInvKin:
 
     def get_dq_cmd(self):
         return self.dq_cmd
+
+
+class BatchedWbcTick:
+    """B robots' ``wbc_controller.compute`` (reference scripts/QP_WBC.py:52-131): Solo12 kinematics / RNEA, InvKin,
+    QPWBC and the feed-forward torque in three kernels.  compute(q, dq, f_cmd, contacts, pgoals, vgoals, agoals) with
+    q [B,19], dq [B,18], f_cmd [B,12], contacts [B,4], goals [B,12] (3x4 column-major); results in tau_ff, qdes, vdes,
+    f_with_delta, ddq_cmd ([B,12] each)."""
+
+    def __init__(self, batch, device=0):
+        self._L = load_library()
+        self.B, self.device = int(batch), int(device)
+        h = C.c_void_p()
+        check(self._L.qrw_wbctick_create(C.byref(h), self.B, self.device))
+        self._h = h
+        self.tau_ff = self.qdes = self.vdes = self.f_with_delta = self.ddq_cmd = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.qrw_wbctick_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def compute(self, q, dq, f_cmd, contacts, pgoals, vgoals, agoals, fetch=True):
+        B = self.B
+        sizes = [19, 18, 12, 4, 12, 12, 12]
+        args = [q, dq, f_cmd, contacts, pgoals, vgoals, agoals]
+        if _is_cuda_tensor(q):
+            check(self._L.qrw_wbctick_run_device(self._h, *[_dev_ptr(a, B * s) for a, s in zip(args, sizes)], _torch_stream()))
+            return 0
+        a = [_host(x, B * s) for x, s in zip(args, sizes)]
+        check(self._L.qrw_wbctick_run_host(self._h, *[x.ctypes.data for x in a]))
+        if fetch:
+            outs = [np.empty((B, 12)) for _ in range(5)]
+            check(self._L.qrw_wbctick_result_host(self._h, *[o.ctypes.data for o in outs]))
+            self.tau_ff, self.qdes, self.vdes, self.f_with_delta, self.ddq_cmd = outs
+        return 0
+
+    def result_tensors(self):
+        """Zero-copy torch views (tau_ff, qdes, vdes, f_res), [B,12] each."""
+        import torch
+
+        ps = [C.c_void_p() for _ in range(4)]
+        check(self._L.qrw_wbctick_result_device(self._h, *[C.byref(p) for p in ps]))
+        return [torch.as_tensor(_DevView(p.value, (self.B, 12)), device=f"cuda:{self.device}") for p in ps]
+
+    def debug(self):
+        Jc, r, d = np.empty((self.B, 216)), np.empty((self.B, 6)), np.empty((self.B, 6))
+        check(self._L.qrw_wbctick_debug_host(self._h, Jc.ctypes.data, r.ctypes.data, d.ctypes.data))
+        return dict(Jc=Jc, RNEA=r, ddq_res=d)
+
+
+def solo12_feet(q12, dq12):
+    """Fixed-base foot kinematics (reference scripts/solo12InvKin.py:47-59) on the GPU: posf, vf, wf, af [B,12], Jf [B,144]."""
+    L = load_library()
+    q12, dq12 = np.ascontiguousarray(q12, np.float64), np.ascontiguousarray(dq12, np.float64)
+    B = q12.size // 12
+    outs = [np.empty((B, 12)) for _ in range(4)] + [np.empty((B, 144))]
+    check(L.qrw_solo12_feet_host(B, q12.ctypes.data, dq12.ctypes.data, *[o.ctypes.data for o in outs]))
+    return outs
+
+
+def solo12_base_inertia():
+    L = load_library()
+    Y = np.empty(6)
+    check(L.qrw_solo12_base_inertia(Y.ctypes.data))
+    return Y

@@ -248,3 +248,42 @@ def invkin_inputs(B, seed):
         Jf[:, 3 * i:3 * i + 3, 3 * i:3 * i + 3] += 0.16 * np.eye(3) + rng.uniform(-0.08, 0.08, (B, 3, 3))
     return (contacts, pack_cols(goals), pack_cols(vgoals), pack_cols(agoals), pack_cols(posf), pack_cols(vf),
             pack_cols(wf), pack_cols(af), pack_cols(Jf))
+
+
+Q_INIT = np.array([0.0, 0.7, -1.4, 0.0, 0.7, -1.4, 0.0, -0.7, 1.4, 0.0, -0.7, 1.4])  # scripts/main_solo12_control.py q_init
+
+
+def wbc_tick_inputs(B, seed, level_base=True):
+    """Inputs of wbc_controller.compute (scripts/QP_WBC.py:52) for B robots, BASELINE config 4:
+    q [B,19] (base at h_ref; identity orientation as scripts/Controller.py:275-283 does, or a small random tilt),
+    dq [B,18], f_cmd [B,12], contacts [B,4], pgoals / vgoals / agoals [B,12] (3x4 column-major)."""
+    rng = np.random.default_rng(seed)
+    q = np.zeros((B, 19))
+    q[:, 2] = H_REF
+    q[:, 6] = 1.0
+    if not level_base:
+        ax = rng.normal(size=(B, 3))
+        ax /= np.linalg.norm(ax, axis=1, keepdims=True)
+        ang = rng.uniform(-0.2, 0.2, B)
+        q[:, 3:6] = ax * np.sin(ang / 2)[:, None]
+        q[:, 6] = np.cos(ang / 2)
+    q[:, 7:] = Q_INIT + rng.uniform(-0.3, 0.3, (B, 12))
+    dq = np.zeros((B, 18))
+    dq[:, 0:3] = rng.uniform(-0.5, 0.5, (B, 3))
+    dq[:, 3:6] = rng.uniform(-0.5, 0.5, (B, 3))
+    dq[:, 6:] = rng.uniform(-3.0, 3.0, (B, 12))
+    contacts = (rng.uniform(size=(B, 4)) > 0.35).astype(np.float64)
+    contacts[contacts.sum(1) == 0, 0] = 1.0
+    nc = contacts.sum(1, keepdims=True)
+    f = np.zeros((B, 4, 3))
+    f[..., 2] = MASS * 9.81 / nc + rng.uniform(-1.0, 1.0, (B, 4))
+    f[..., 0:2] = rng.uniform(-0.3, 0.3, (B, 4, 2)) * f[..., 2:3]
+    f *= contacts[..., None]
+    # foot goals around the nominal stance (shoulders, ground at -h_ref)
+    goals = np.zeros((B, 3, 4))
+    goals[:, 0] = SHOULDERS[0] + rng.uniform(-0.03, 0.03, (B, 4))
+    goals[:, 1] = SHOULDERS[1] + rng.uniform(-0.03, 0.03, (B, 4))
+    goals[:, 2] = -0.22 + rng.uniform(-0.03, 0.03, (B, 4))
+    vgoals = rng.uniform(-0.5, 0.5, (B, 3, 4))
+    agoals = rng.uniform(-5.0, 5.0, (B, 3, 4))
+    return q, dq, f.reshape(B, 12), contacts, pack_cols(goals), pack_cols(vgoals), pack_cols(agoals)

@@ -45,3 +45,17 @@ def test_wbc_invkin_golden():
     ik.refreshAndCompute(*[k[n] for n in names])
     for a, n in zip((ik.ddq, ik.dq_cmd, ik.q_step), ("ddq", "dq_cmd", "q_step")):
         np.testing.assert_allclose(a, k[n], rtol=1e-12, atol=1e-12)
+
+
+def test_wbc_tick_golden():
+    from qrw_b200 import BatchedWbcTick
+
+    g = np.load(os.path.join(GOLD, "wbc_tick_b16.npz"))
+    t = BatchedWbcTick(16)
+    names = ["q", "dq", "f_cmd", "contacts", "pgoals", "vgoals", "agoals"]
+    for c in range(2):
+        t.compute(*[g[f"{n}{c}"] for n in names])
+        assert_forces_close(t.f_with_delta, g[f"f_res{c}"], f"f_with_delta call {c}")
+        np.testing.assert_allclose(t.tau_ff, g[f"tau_ff{c}"], rtol=1e-5, atol=1e-4)
+        np.testing.assert_allclose(t.qdes, g[f"qdes{c}"], rtol=1e-10, atol=1e-10)
+        np.testing.assert_allclose(t.vdes, g[f"vdes{c}"], rtol=1e-10, atol=1e-10)

@@ -169,3 +169,13 @@ def test_oracle_reproduces_wbc_invkin_golden(oracle):
     outs = oracle.invkin(*[k[n] for n in names])
     for a, n in zip(outs, ("ddq", "dq_cmd", "q_step")):
         np.testing.assert_allclose(a, k[n], rtol=1e-13, atol=1e-13)
+
+
+def test_oracle_reproduces_wbc_tick_golden(oracle):
+    g = np.load(os.path.join(GOLD, "wbc_tick_b16.npz"))
+    o = oracle.OracleWBC(16)
+    names = ["q", "dq", "f_cmd", "contacts", "pgoals", "vgoals", "agoals"]
+    for c in range(2):
+        r = oracle.wbc_tick(o, *[g[f"{n}{c}"] for n in names], nthreads=4)
+        for k in ("tau_ff", "qdes", "vdes", "f_res"):
+            np.testing.assert_allclose(r[k], g[f"{k}{c}"], rtol=0, atol=1e-9)

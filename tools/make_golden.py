@@ -65,6 +65,16 @@ def main():
     names = ["contacts", "goals", "vgoals", "agoals", "posf", "vf", "wf", "af", "Jf"]
     np.savez_compressed(os.path.join(OUT, "invkin_b16.npz"), **dict(zip(names, args)),
                         ddq=outs[0], dq_cmd=outs[1], q_step=outs[2])
+    # whole-body tick (Solo12 kinematics / RNEA + InvKin + QPWBC + tau_ff), two calls
+    o = ob.OracleWBC(B)
+    rec = {}
+    names = ["q", "dq", "f_cmd", "contacts", "pgoals", "vgoals", "agoals"]
+    for c in range(2):
+        args = wl.wbc_tick_inputs(B, seed=50 + c, level_base=(c == 0))
+        r = ob.wbc_tick(o, *args, nthreads=4)
+        rec.update({f"{n}{c}": a for n, a in zip(names, args)})
+        rec.update({f"{k}{c}": v for k, v in r.items()})
+    np.savez_compressed(os.path.join(OUT, "wbc_tick_b16.npz"), **rec)
     print("wrote", sorted(os.listdir(OUT)))
 
 
