@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = 48 per host thread)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wbc-batch", type=int, default=65536, help="robots in the whole-body-tick leg (BASELINE config 4); 0 skips it")
     return ap.parse_args()
 
 
@@ -230,7 +231,7 @@ def run_b200(args):
         ev[s][0].record()
         mpc.run(W + s + 1, *dev_in[W + s])
         if world > 1:  # the one exchange of the path: first-step contact forces of every robot
-            dist.all_gather(gather, res[:, 12:24].contiguous())
+            dist.all_gather(gather, res[:, 12:24].contiguous())  # = fleet.gather_rows for equal shards
         ev[s][1].record()
     barrier()
     wall_dev = time.perf_counter() - t_wall0
@@ -263,6 +264,58 @@ def run_b200(args):
     e2e_value = world * B * K / float(e2e_t.item())
     h2d = int(pin_x.nbytes + pin_f.nbytes)
     d2h = int(pin_r.nbytes)
+
+    # ---- leg 3 (auxiliary, BASELINE configs 4 and 5): whole-body tick alone on 65536 robots, and the full control
+    #      tick (MPC update solve + whole-body tick fed with the MPC's first-step forces) on the MPC batch
+    aux = {}
+    if args.wbc_batch > 0:
+        from qrw_b200 import BatchedWbcTick
+        from qrw_b200 import fleet
+
+        Bw = args.wbc_batch
+        tick = BatchedWbcTick(Bw, device=local)
+        targs = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in wl.wbc_tick_inputs(Bw, seed=3 + rank)]
+        for _ in range(3):
+            tick.compute(*targs)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        flush.fill_(1)
+        e0.record()
+        for _ in range(reps):
+            tick.compute(*targs)
+        e1.record()
+        barrier()
+        wt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(wt, op=dist.ReduceOp.MAX)
+        wbc_ms = float(wt.item()) / reps
+        wbc_bytes = 1240  # 712 B in + 528 B out per tick through the batched-native API
+        aux["wbc_tick"] = {"value": world * Bw / (wbc_ms * 1e-3), "unit": "ticks/s", "robots_per_gpu": Bw, "ms_per_step": wbc_ms,
+                           "kernels_per_step": 3, "hbm_GBps_algorithmic": wbc_bytes * Bw / (wbc_ms * 1e-3) / 1e9,
+                           "hbm_frac_of_measured": wbc_bytes * Bw / (wbc_ms * 1e-3) / 1e9 / measured_peaks()[0]["hbm_gbs"],
+                           "workload": "BASELINE config 4: Solo12 kinematics/RNEA + InvKin + QPWBC + tau_ff, inputs resident in HBM"}
+        # full control tick on the MPC batch: MPC update solve, then the whole-body tick with f_cmd = first-step forces
+        tickm = BatchedWbcTick(B, device=local)
+        margs = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in wl.wbc_tick_inputs(B, seed=5 + rank)]
+        mpc.state_load(snap)
+        for t in range(W):
+            mpc.run(t + 1, *dev_in[t])
+            margs[2] = fleet.first_step_forces(res).contiguous()
+            tickm.compute(*margs)
+        barrier()
+        e0.record()
+        for s_ in range(K):
+            mpc.run(W + s_ + 1, *dev_in[W + s_])
+            margs[2] = fleet.first_step_forces(res).contiguous()
+            tickm.compute(*margs)
+        e1.record()
+        barrier()
+        ft = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ft, op=dist.ReduceOp.MAX)
+        aux["full_tick"] = {"value": world * B * K / (float(ft.item()) * 1e-3), "unit": "ticks/s", "robots_per_gpu": B,
+                            "workload": "BASELINE config 5 shape: one MPC update solve + one whole-body tick per robot and step"}
 
     # ---- roofline of the dominant kernel (the only kernel in a step)
     peaks, which = measured_peaks()
@@ -304,6 +357,7 @@ def run_b200(args):
                        "p99": float(np.percentile(timed_iters, 99)), "max": int(timed_iters.max())},
         "solved_frac": float((status == 1).mean()), "wall_s_device_leg": wall_dev,
     }
+    line.update(aux)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
