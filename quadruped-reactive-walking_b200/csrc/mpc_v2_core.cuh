@@ -71,12 +71,12 @@ struct Sm {
 QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
 
 // per-thread registers of variable lane j = 3 foot + axis of stage k (lanes 12..15 of a stage idle):
-//   bc[0..2] = B_k(9..11, j), gf[0..5] = column j of GF (rows 6..11); row j of F_k^-1 lives in the record (R_FI)
+//   bc[0..2] = B_k(9..11, j); row j of F_k^-1 and GF live in the record (R_FI, R_GF)
 //   xf, xX: scaled iterates of f_k[j], X_{k+1}[j]; z1, y1, e1: dynamics row (k,j); y2: force-enable row (k,j)
 //   friction-cone rows of the foot, two slots: axis x -> rows 0,1 (+-fx - mu fz), axis y -> rows 2,3, axis z -> row 4 (-fz)
 //   in slot A and nothing in slot B
 struct Regs {
-  double bc[3], gf[6];
+  double bc[3];
   double xf, xX, dF, dX, z1, y1, e1, y2;
   double zA, yA, eA, zB, yB, eB;
 };
@@ -193,7 +193,6 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
     for (int r = 0; r < 6; ++r) {
       Y[6 * j + r] = y[r];
       const double g = Ek[6 + r] * y[r];  // GF(6+r, j) = E (B0 D_f F^-1)(6+r, j), F^-1 symmetric
-      R.gf[r] = g;
       rec[R_GF + LD * r + j] = g;
     }
   }
@@ -457,8 +456,6 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   for (int i = tid; i < 576; i += NT) S.rec[SR * (i / 36) + R_BANG + (i % 36)] = first ? 0.0 : st_d[ST_BANG + i];
   if (tid < 32) gait[tid] = first ? 0 : st_i[tid];
   if (tid < NS) sb[tid] = first ? 0 : st_i[32 + tid];
-#pragma unroll
-  for (int t = 0; t < 6; ++t) R.gf[t] = 0.0;
   R.bc[0] = R.bc[1] = R.bc[2] = 0.0;
   R.xf = R.xX = R.z1 = R.y1 = R.y2 = R.zA = R.yA = R.zB = R.yB = 0.0;
   if (!first && isv) {
@@ -681,7 +678,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     cscale *= 1.0 / c_temp;
   }
   cta::bar();
-  const double cinv = 1.0 / cscale;
+  if (tid == 0) S.red[120] = cscale;
   if (dbg && isv) {
     dbg[gvar(k, j)] = R.dF;
     dbg[gvar(k, 12 + j)] = R.dX;
@@ -706,7 +703,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   int iter = 0;
   for (iter = 1; iter <= C.max_iter; ++iter) {
     if (refactor) {
-      factor(C, S, R, Rh, cscale, tid);
+      factor(C, S, R, Rh, S.red[120], tid);
       ++n_factor;
       refactor = false;
     }
@@ -725,9 +722,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     // (2) t_f = sigma x_f + D_f (A' u)_f
     if (isv) {
       double v = C.dtm * BAk[6 + c3];
-      v += R.bc[0] * BAk[9];
-      v += R.bc[1] * BAk[10];
-      v += R.bc[2] * BAk[11];
+      v += Bk[j] * BAk[9];
+      v += Bk[12 + j] * BAk[10];
+      v += Bk[24 + j] * BAk[11];
       if (bit) v += u2;
       if (c3 < 2)
         v += uA - uB;
@@ -797,7 +794,8 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     double xtf = 0.0, zt = rX;
     if (isv) {
       const double r0 = BAk[6], r1 = BAk[7], r2 = BAk[8], r3 = BAk[9], r4 = BAk[10], r5 = BAk[11];
-      const double s0 = (R.gf[0] * r0 + R.gf[1] * r1) + (R.gf[2] * r2 + R.gf[3] * r3) + (R.gf[4] * r4 + R.gf[5] * r5);
+      const double* gc = rec + R_GF + j;  // column j of GF
+      const double s0 = (gc[0] * r0 + gc[LD] * r1) + (gc[2 * LD] * r2 + gc[3 * LD] * r3) + (gc[4 * LD] * r4 + gc[5 * LD] * r5);
       xtf = uf - Rh.rho_eq * s0;
       BCk[j] = R.dF * xtf;
       if (j >= 6) {
@@ -854,6 +852,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         BDk[j] = yA + yB;
       }
       cta::bar();
+      const double cscale = S.red[120], cinv = 1.0 / cscale;
       double m[12];
 #pragma unroll
       for (int q = 0; q < 12; ++q) m[q] = 0.0;
@@ -890,9 +889,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         // force variable
         const double* u = rec + R_A;
         double v = C.dtm * u[6 + c3];
-        v += R.bc[0] * u[9];
-        v += R.bc[1] * u[10];
-        v += R.bc[2] * u[11];
+        v += Bk[j] * u[9];
+        v += Bk[12 + j] * u[10];
+        v += Bk[24 + j] * u[11];
         if (bit) v += BBk[j];
         if (c3 < 2)
           v += yA - yB;
