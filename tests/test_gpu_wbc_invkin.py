@@ -35,3 +35,30 @@ def test_invkin_matches_oracle(oracle):
     np.testing.assert_allclose(ik.ddq, ddq, rtol=1e-11, atol=1e-9)
     np.testing.assert_allclose(ik.get_dq_cmd(), dq, rtol=1e-11, atol=1e-11)
     np.testing.assert_allclose(ik.get_q_step(), qs, rtol=1e-11, atol=1e-12)
+
+
+def test_drop_in_module_classes(oracle):
+    """The Boost.Python-shaped module (python/gepadd.cpp:178-238): one robot, natural (rows x cols) numpy matrices in,
+    the reference's getter shapes out."""
+    import libquadruped_reactive_walking as lrw
+    from qrw_b200 import workloads as wl
+    from qrw_b200.batched import unpack_cols
+
+    M, Jc, f, R = wl.wbc_inputs(1, seed=77)
+    q = lrw.QPWBC()
+    assert q.run(unpack_cols(M, 18, 18)[0], unpack_cols(Jc, 12, 18)[0], f.reshape(12, 1), R.reshape(6, 1), np.zeros((1, 4))) == 0
+    o = oracle.OracleWBC(1)
+    o.run(M, Jc, f, R)
+    fc, dc, Hc = o.results()
+    assert q.get_f_res().shape == (12, 1) and q.get_ddq_res().shape == (6, 1) and q.get_H().shape == (12, 12)
+    assert_forces_close(q.get_f_res().ravel(), fc.ravel(), "QPWBC.get_f_res")
+    np.testing.assert_allclose(q.get_H(), Hc.reshape(12, 12).T, rtol=1e-12, atol=1e-12)
+    args = wl.invkin_inputs(1, seed=78)
+    shapes = [(1, 4), (3, 4), (3, 4), (3, 4), (4, 3), (4, 3), (4, 3), (4, 3), (12, 12)]
+    nat = [unpack_cols(a, r, c)[0] for a, (r, c) in zip(args, shapes)]
+    ik = lrw.InvKin(0.002)
+    ddq = ik.refreshAndCompute(*nat)
+    ref = oracle.invkin(*args)
+    assert ddq.shape == (12, 1) and ik.get_q_step().shape == (12, 1)
+    np.testing.assert_allclose(ddq.ravel(), ref[0].ravel(), rtol=1e-11, atol=1e-9)
+    np.testing.assert_allclose(ik.get_dq_cmd().ravel(), ref[1].ravel(), rtol=1e-11, atol=1e-11)
