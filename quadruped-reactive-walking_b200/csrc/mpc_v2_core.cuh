@@ -9,16 +9,19 @@
 // with 534 local-memory loads per ADMM iteration, 15.2 k warp instructions per iteration, issue slots 21 % busy.
 // Its block-tridiagonal solve applies a dense 24x24 pivot inverse three times per stage and iteration.  Here
 //   * the reduced KKT matrix K = P + sigma I + A' diag(rho) A is eliminated FORCES FIRST: the 16 force
-//     blocks F_k (12x12, independent of one another) go first, the Schur complement on the states is block
-//     tridiagonal with 12x12 blocks (pivot inverses Sig_k, recurrence matrices T_k = Sig_k G_{k,k+1}).  An
-//     iteration needs 2 x 16 products with F_k^-1 (rows in REGISTERS of the row owner), 16 with Sig_k and
-//     2 x 15 with T_k (shared memory): 11 k FMA instead of 32 k, and 72 KB of shared memory so that THREE CTAs
-//     (24 warps) are resident per SM;
+//     blocks F_k (12x12, independent of one another) go first; the Schur complement on the states is block
+//     tridiagonal with 12x12 blocks and is factored TWISTED (stages 0..7 downwards, 15..9 upwards, stage 8
+//     last), so that a solve runs two 7-step elimination chains and two 8-step back-substitution chains at
+//     once in the two half-warps of one warp (17 sequential 12x12 products instead of 31).  GF = E B0 D_f F^-1
+//     and M = GF D_f B0' E are formed at factorisation time: one broadcast of the force right-hand side gives
+//     u = F^-1 t and what the dynamics rows see of it, one broadcast of the six dynamics-row residuals gives
+//     x~_f and z~.  About 5 k warp instructions per ADMM iteration instead of 15 k;
 //   * 16 lanes per horizon stage: lane j < 12 of stage k owns force f_k[j], state X_{k+1}[j], dynamics row
-//     (k,j) and force-enable row (k,j); lane 12+f owns the five friction-cone rows of foot f.  All iterates
-//     live in registers of their owner; stage-internal exchanges go through 16-double shared buffers and
-//     __syncwarp, only the state recurrence (one warp, 24 lanes, 15 + 15 steps) needs the two CTA barriers
-//     of an iteration.
+//     (k,j), force-enable row (k,j) and up to two friction-cone rows of its foot; lanes 12..15 idle.  The
+//     iterates live in registers of their owner; everything else a stage owns (exchange buffers, D, E, B_k,
+//     F^-1, GF, M) sits in one shared-memory record.  Stage-internal exchanges use __syncwarp; only the
+//     state chain (a noinline call, one warp) needs the two CTA barriers of an iteration.
+//   * 108 KB of shared memory and 128 registers: two CTAs (16 warps) per SM.
 // It is still an exact solve of the same KKT system: the iterates differ from OSQP's by round-off only.
 #pragma once
 #include "mpc_core.cuh"
@@ -97,10 +100,10 @@ QRW_HD double b0_row(const MpcConst& C, const double* Bk, const double* v, int r
 
 // ------------------------------------------------------------------------------------------
 // Factorisation of K, forces first.  All threads of the CTA; ends with a CTA barrier.
-//   F_k   = K(f_k, f_k)                                   -> R.q[0..11] (row j of the inverse)
+//   F_k   = K(f_k, f_k)                                   -> record (R_FI: inverse; R_GF, R_MR: GF and M)
 //   N_k   = e^2 (B0 D_f F_k^-1 D_f B0') e^2  (6 x 6)      -> record scratch
-//   G_kk, G_{k,k+1}: Schur complement on the states       -> Sig / T slots, then
-//   Sig_k = (G_kk - G_{k-1,k}' Sig_{k-1} G_{k-1,k})^-1,  T_k = Sig_k G_{k,k+1}
+//   G_kk, G_{k,k+1}: Schur complement on the states       -> Sig / T slots, then the twisted block LDL'
+//   (pivot inverses Sig_k, coupling matrices T_k = Sig_k G_{k,k+1} for k <= 7, U_k = Sig_k G_{k-1,k}' for k >= 9)
 // ------------------------------------------------------------------------------------------
 QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, double cscale, int tid) {
   const int k = tid >> 4, j = tid & 15;
@@ -215,7 +218,7 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
       rec[R_MR + e] = er * acc * erp;
     }
   }
-  cta::wsync();  // N overlaps the tail of Y: everybody has read Y
+  cta::wsync();
   if (isv) {
 #pragma unroll
     for (int t = 0; t < 3; ++t) N[3 * j + t] = nv[t];
