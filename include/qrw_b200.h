@@ -139,6 +139,57 @@ int qrw_solo12_base_inertia(double* Y6);
 int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, double* posf, double* vf, double* wf,
                          double* af, double* Jf);
 
+/* ---------------------------------------------------------------------------------------
+ * Planners -- the input producers of the MPC and of the whole-body tick for B robots:
+ *   Gait::updateGait                       src/Gait.cpp:189-260           (stage bit 1)
+ *   FootstepPlanner::updateFootsteps       src/FootstepPlanner.cpp:52-75  (stage bit 2)
+ *   FootTrajectoryGenerator::update        src/FootTrajectoryGenerator.cpp:110-151 (stage bit 4)
+ *   StatePlanner::computeReferenceStates   src/StatePlanner.cpp:22-60     (stage bit 8)
+ *   feet commands in the base frame        scripts/Controller.py:286-296  (stage bit 16)
+ * One call = one control tick k of scripts/Controller.py:222-240 with the stages selected by the mask, in that order;
+ * xref / fsteps come out in the layout qrw_mpc_run_device reads, contacts / p_cmd / v_cmd / a_cmd in the layout
+ * qrw_wbctick_run_device reads, so a closed-loop batch never leaves HBM.
+ * ------------------------------------------------------------------------------------- */
+typedef struct qrw_planner qrw_planner_t;
+#define QRW_PLAN_GAIT 1
+#define QRW_PLAN_FOOTSTEPS 2
+#define QRW_PLAN_FOOTTRAJ 4
+#define QRW_PLAN_STATE 8
+#define QRW_PLAN_FEETCMD 16
+#define QRW_PLAN_ALL 31
+/* Gait::initialize(dt_mpc, T_gait, T_mpc, N_gait) (Gait.cpp:21-36: trot, fails where the reference throws),
+ * StatePlanner::initialize(dt_mpc, T_mpc, h_ref), FootstepPlanner::initialize(dt_mpc, dt_wbc, T_mpc, h_ref, shoulders, gait,
+ * N_gait), FootTrajectoryGenerator::initialize(0.05, 0.07, shoulders, shoulders, dt_wbc, k_mpc, gait) with the shoulders
+ * of scripts/Controller.py:131-139. */
+int qrw_planner_create(qrw_planner_t** out, int batch, double dt_mpc, double dt_wbc, double T_gait, double T_mpc, int N_gait,
+                       int k_mpc, double h_ref, int device);
+int qrw_planner_destroy(qrw_planner_t* h);
+/* other initialize() arguments (host pointers to 3 x 4 column-major matrices shared by the batch, NULL keeps the current
+ * value); resets every robot to its initial state */
+int qrw_planner_configure(qrw_planner_t* h, const double* shoulders, const double* ftg_target, const double* ftg_position,
+                          double max_height, double lock_time);
+/* q7 [B][7] = q.head(7) (x y z, quaternion x y z w), v6 [B][6] = h_v, vref6 [B][6], code [B] joystick codes of
+ * Gait::changeGait (NULL = 0; 5 = Gait::create_walk, an extension). */
+int qrw_planner_run_device(qrw_planner_t* h, int k, int stages, const double* q7, const double* v6, const double* vref6,
+                           const int* code, void* stream);
+int qrw_planner_run_host(qrw_planner_t* h, int k, int stages, const double* q7, const double* v6, const double* vref6,
+                         const int* code);
+/* StatePlanner::getReferenceStates [B][12*(n+1)], FootstepPlanner::getFootsteps [B][N_gait*12], currentGait_.row(0)
+ * [B][4], o_targetFootstep_, FootTrajectoryGenerator::getFootPosition / Velocity / Acceleration, feet_p/v/a_cmd: [B][12]
+ * (3 x 4 column-major).  Any pointer may be NULL. */
+int qrw_planner_outputs_device(qrw_planner_t* h, const double** xref, const double** fsteps, const double** contacts,
+                               const double** o_target, const double** fpos, const double** fvel, const double** facc,
+                               const double** p_cmd, const double** v_cmd, const double** a_cmd);
+/* same on the host; gait = Gait::getCurrentGait [B][N_gait*4] */
+int qrw_planner_outputs_host(qrw_planner_t* h, double* xref, double* fsteps, double* gait, double* o_target, double* fpos,
+                             double* fvel, double* facc, double* p_cmd, double* v_cmd, double* a_cmd);
+/* internal state: pastGait_ / desiredGait_ [B][N_gait*4], currentFootstep_ [B][12], t0s / t_swing [B][4],
+ * flags [B][2] = (Gait::isNewPhase, Gait::getIsStatic) */
+int qrw_planner_state_host(qrw_planner_t* h, double* past_gait, double* desired_gait, double* current_footstep, double* t0s,
+                           double* t_swing, int* flags);
+/* the `targetFootstep` argument of FootTrajectoryGenerator::update for callers that run stage 4 on its own: [B][12] */
+int qrw_planner_set_target_host(qrw_planner_t* h, const double* o_target);
+
 #ifdef __cplusplus
 }
 #endif

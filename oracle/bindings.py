@@ -67,6 +67,16 @@ def lib():
         L.orc_solo12_rnea.argtypes = [C.c_int] + [_dp] * 4
         L.orc_solo12_jc.argtypes = [C.c_int] + [_dp] * 3
         L.orc_solo12_crba.argtypes = [_dp, _dp]
+        L.orc_planner_create.restype = C.c_void_p
+        L.orc_planner_create.argtypes = [C.c_int] + [C.c_double] * 4 + [C.c_int, C.c_int, C.c_double, _dp, _dp, _dp,
+                                                                         C.c_double, C.c_double]
+        L.orc_planner_destroy.argtypes = [C.c_void_p]
+        L.orc_planner_run.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp, _dp, _ip]
+        L.orc_planner_outputs.argtypes = [C.c_void_p] + [_dp] * 7
+        L.orc_planner_state.argtypes = [C.c_void_p] + [_dp] * 5 + [_ip]
+        L.orc_planner_phase_duration.restype = C.c_double
+        L.orc_planner_phase_duration.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, _dp]
+        L.orc_planner_create_walk.argtypes = [C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -307,3 +317,76 @@ def ref_st_to_cc(rows, cols, vals, n_cols):
     p = values(nst, _i(rows), _i(cols), _d(vals), ncc, n_cols, _i(icc), _i(ccc))
     acc = np.array([p[k] for k in range(ncc)])
     return icc, ccc, acc
+
+
+SHOULDERS34 = np.array([0.1946, 0.14695, 0.0, 0.1946, -0.14695, 0.0, -0.1946, 0.14695, 0.0, -0.1946, -0.14695, 0.0])
+
+
+class OraclePlanner:
+    """Batch of restated Gait + StatePlanner + FootstepPlanner + FootTrajectoryGenerator objects wired as
+    scripts/Controller.py:124-139 (oracle/planner_oracle.cpp).  run(k, ...) = Controller.py:222-236 for tick k."""
+
+    GAIT, FOOTSTEPS, FOOTTRAJ, STATE = 1, 2, 4, 8
+
+    def __init__(self, batch, dt_mpc=0.02, dt_wbc=0.002, T_gait=0.32, T_mpc=0.32, N_gait=20, k_mpc=10, h_ref=0.2447495,
+                 shoulders=None, ftg_target=None, ftg_pos=None, max_height=0.05, lock_time=0.07):
+        sh = _c(SHOULDERS34 if shoulders is None else shoulders).ravel()
+        tg = _c(sh if ftg_target is None else ftg_target).ravel()
+        ps = _c(sh if ftg_pos is None else ftg_pos).ravel()
+        self.B, self.N_gait, self.n = batch, N_gait, int(round(T_mpc / dt_mpc))
+        self.h = lib().orc_planner_create(batch, dt_mpc, dt_wbc, T_gait, T_mpc, N_gait, k_mpc, h_ref, _d(sh), _d(tg), _d(ps),
+                                          max_height, lock_time)
+        if not self.h:
+            raise ValueError("Sizes of matrices are too small for considered durations. Increase N_gait in config file.")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_planner_destroy(self.h)
+            self.h = None
+
+    def run(self, k, q7, v6, vref6, code=None, stages=15):
+        q7, v6, vref6 = _c(q7), _c(v6), _c(vref6)
+        assert q7.size == 7 * self.B and v6.size == 6 * self.B and vref6.size == 6 * self.B
+        cd = None if code is None else np.ascontiguousarray(code, np.int32)
+        lib().orc_planner_run(self.h, int(k), int(stages), _d(q7), _d(v6), _d(vref6), None if cd is None else _i(cd))
+
+    def outputs(self):
+        B, N = self.B, self.N_gait
+        o = dict(xref=np.empty((B, 12 * (self.n + 1))), fsteps=np.empty((B, 12 * N)), gait=np.empty((B, 4 * N)),
+                 o_target=np.empty((B, 12)), fpos=np.empty((B, 12)), fvel=np.empty((B, 12)), facc=np.empty((B, 12)))
+        lib().orc_planner_outputs(self.h, *[_d(o[k]) for k in ("xref", "fsteps", "gait", "o_target", "fpos", "fvel", "facc")])
+        return o
+
+    def state(self):
+        B, N = self.B, self.N_gait
+        s = dict(past=np.empty((B, 4 * N)), desired=np.empty((B, 4 * N)), cur_fs=np.empty((B, 12)), t0s=np.empty((B, 4)),
+                 t_swing=np.empty((B, 4)))
+        fl = np.empty((B, 2), np.int32)
+        lib().orc_planner_state(self.h, *[_d(s[k]) for k in ("past", "desired", "cur_fs", "t0s", "t_swing")], _i(fl))
+        s["flags"] = fl
+        return s
+
+    def phase_duration(self, b, i, j, value):
+        rem = np.zeros(1)
+        t = lib().orc_planner_phase_duration(self.h, b, i, j, float(value), _d(rem))
+        return t, rem[0]
+
+
+def feet_commands(pos, vel, acc, q7, vref6, p_prev, v_prev, h_ref):
+    """Controller.py:286-296 for a batch: feet position / velocity / acceleration commands in the base frame from the
+    FootTrajectoryGenerator outputs ([B,12], 3x4 column-major), with oRh = Rz(yaw(q)), oTh = (x, y, 0) (:419-423)."""
+    B = pos.shape[0]
+    x, y, z, w = q7[:, 3], q7[:, 4], q7[:, 5], q7[:, 6]
+    yaw = np.arctan2(2 * (x * y + z * w), 1 - 2 * (y * y + z * z))
+    c, s = np.cos(yaw), np.sin(yaw)
+    RT = np.zeros((B, 3, 3))
+    RT[:, 0, 0], RT[:, 0, 1], RT[:, 1, 0], RT[:, 1, 1], RT[:, 2, 2] = c, s, -s, c, 1.0
+    P, V, A = (a.reshape(B, 4, 3) for a in (pos, vel, acc))
+    pp, vp = p_prev.reshape(B, 4, 3), v_prev.reshape(B, 4, 3)
+    wv = np.broadcast_to(vref6[:, None, 3:6], (B, 4, 3))
+    a_cmd = np.einsum("bij,bfj->bfi", RT, A) - np.cross(wv, np.cross(wv, pp)) - 2 * np.cross(wv, vp)
+    v_cmd = np.einsum("bij,bfj->bfi", RT, V) - vref6[:, None, 0:3] - np.cross(wv, pp)
+    off = np.zeros((B, 1, 3))
+    off[:, 0, 0], off[:, 0, 1], off[:, 0, 2] = q7[:, 0], q7[:, 1], h_ref
+    p_cmd = np.einsum("bij,bfj->bfi", RT, P - off)
+    return p_cmd.reshape(B, 12), v_cmd.reshape(B, 12), a_cmd.reshape(B, 12)

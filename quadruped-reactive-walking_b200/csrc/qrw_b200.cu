@@ -1017,3 +1017,4 @@ int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, doubl
 }
 
 }  // extern "C"
+#include "planner_abi.cuh"

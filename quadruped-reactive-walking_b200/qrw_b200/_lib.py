@@ -82,6 +82,16 @@ _SIGNATURES = {
     "qrw_wbctick_debug_host": (C.c_int, [_vp] * 4),
     "qrw_solo12_base_inertia": (C.c_int, [_vp]),
     "qrw_solo12_feet_host": (C.c_int, [C.c_int] + [_vp] * 7),
+    "qrw_planner_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
+                                     C.c_double, C.c_int]),
+    "qrw_planner_destroy": (C.c_int, [_vp]),
+    "qrw_planner_configure": (C.c_int, [_vp, _vp, _vp, _vp, C.c_double, C.c_double]),
+    "qrw_planner_run_device": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "qrw_planner_run_host": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp]),
+    "qrw_planner_outputs_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 10),
+    "qrw_planner_outputs_host": (C.c_int, [_vp] * 11),
+    "qrw_planner_state_host": (C.c_int, [_vp] * 7),
+    "qrw_planner_set_target_host": (C.c_int, [_vp, _vp]),
 }
 
 

@@ -287,3 +287,58 @@ def wbc_tick_inputs(B, seed, level_base=True):
     vgoals = rng.uniform(-0.5, 0.5, (B, 3, 4))
     agoals = rng.uniform(-5.0, 5.0, (B, 3, 4))
     return q, dq, f.reshape(B, 12), contacts, pack_cols(goals), pack_cols(vgoals), pack_cols(agoals)
+
+
+class PlannerWorkload:
+    """Per-tick inputs of the planners for B robots: what scripts/Controller.py:updateState (:383-425) hands to
+    Gait / FootstepPlanner / StatePlanner each control tick -- the base pose q.head(7) integrated from the velocity
+    reference ("perfect" x, y, yaw; measured height, roll, pitch replaced by seeded noise), the base velocity in the
+    horizontal frame h_v (reference + noise) and the joystick reference v_ref, piecewise constant with a few gait
+    changes (joystick codes of Gait::changeGait; 5 = walk).  Deterministic in (B, seed); tick(k) must be called for
+    k = 0, 1, 2, ... in order."""
+
+    def __init__(self, B, seed, dt_wbc=0.002, k_mpc=10, codes=(1, 2, 3, 4), change_every=170):
+        self.B, self.dt, self.k_mpc = B, dt_wbc, k_mpc
+        self.rng = np.random.default_rng(seed)
+        self.codes, self.change_every = tuple(codes), change_every
+        self.xy = np.zeros((B, 2))
+        self.yaw = self.rng.uniform(-3.0, 3.0, B)
+        self.vref = np.zeros((B, 6))
+        self._new_vref()
+        self.k = 0
+
+    def _new_vref(self):
+        B, r = self.B, self.rng
+        self.vref[:, 0] = r.uniform(-0.5, 1.5, B)
+        self.vref[:, 1] = r.uniform(-0.5, 0.5, B)
+        self.vref[:, 5] = r.uniform(-0.7, 0.7, B)
+        self.vref[r.random(B) < 0.1, 5] = 0.0  # the yaw-rate == 0 branch of the planners
+
+    def tick(self, k):
+        assert k == self.k, "ticks must be consumed in order"
+        B, r = self.B, self.rng
+        code = np.zeros(B, np.int32)
+        if k > 0 and k % self.change_every == 0 and self.codes:
+            pick = r.random(B) < 0.5
+            code[pick] = r.choice(self.codes, pick.sum())
+            self._new_vref()
+        # Controller.py:393-403: perfect integration of x, y, yaw
+        c, s = np.cos(self.yaw), np.sin(self.yaw)
+        self.xy[:, 0] += (c * self.vref[:, 0] - s * self.vref[:, 1]) * self.dt
+        self.xy[:, 1] += (s * self.vref[:, 0] + c * self.vref[:, 1]) * self.dt
+        self.yaw += self.vref[:, 5] * self.dt
+        roll, pitch = r.uniform(-0.1, 0.1, B), r.uniform(-0.1, 0.1, B)
+        q7 = np.zeros((B, 7))
+        q7[:, 0:2] = self.xy
+        q7[:, 2] = r.uniform(0.2, 0.26, B)
+        q7[:, 3:7] = euler_to_quaternion(roll, pitch, self.yaw)
+        h_v = self.vref + r.uniform(-0.1, 0.1, (B, 6))
+        self.k += 1
+        return q7, h_v, self.vref.copy(), code
+
+
+def euler_to_quaternion(roll, pitch, yaw):
+    """(x, y, z, w) of Rz(yaw) Ry(pitch) Rx(roll) -- Estimator.EulerToQuaternion of the reference scripts."""
+    cr, sr, cp, sp, cy, sy = np.cos(roll / 2), np.sin(roll / 2), np.cos(pitch / 2), np.sin(pitch / 2), np.cos(yaw / 2), np.sin(yaw / 2)
+    return np.stack([sr * cp * cy - cr * sp * sy, cr * sp * cy + sr * cp * sy, cr * cp * sy - sr * sp * cy,
+                     cr * cp * cy + sr * sp * sy], axis=-1)
