@@ -320,6 +320,63 @@ def run_b200(args):
         aux["full_tick"] = {"value": world * B * K / (float(ft.item()) * 1e-3), "unit": "ticks/s", "robots_per_gpu": B,
                             "workload": "BASELINE config 5 shape: one MPC update solve + one whole-body tick per robot and step"}
 
+        # planners alone on the config-4 batch: one kernel per control tick, 10 ticks = one MPC period
+        from qrw_b200.controller import BatchedController
+        from qrw_b200.planner import BatchedPlanner
+
+        pw = wl.PlannerWorkload(Bw, 7 + rank, change_every=1000)
+        pin = [[torch.from_numpy(a).to(dev) for a in pw.tick(k)] for k in range(20)]
+        pl = BatchedPlanner(Bw, device=local)
+        for k in range(10):
+            pl.run(k, *pin[k])
+        barrier()
+        flush.fill_(2)
+        e0.record()
+        for k in range(10, 20):
+            pl.run(k, *pin[k])
+        e1.record()
+        barrier()
+        pt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(pt, op=dist.ReduceOp.MAX)
+        plan_ms = float(pt.item()) / 10
+        plan_bytes = 6532  # 1,520 B read + 5,012 B written per robot and tick (xref 1,632 + fsteps 1,920 dominate)
+        aux["planner_tick"] = {"value": world * Bw / (plan_ms * 1e-3), "unit": "ticks/s", "robots_per_gpu": Bw, "ms_per_step": plan_ms,
+                               "kernels_per_step": 1, "hbm_GBps_algorithmic": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9,
+                               "hbm_frac_of_measured": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9 / measured_peaks()[0]["hbm_gbs"],
+                               "workload": "Gait + FootstepPlanner + FootTrajectoryGenerator + StatePlanner + feet commands, inputs resident in HBM"}
+        del pl
+        # closed control loop in HBM at the reference cadence (Controller.py:246: one MPC solve per k_mpc = 10 ticks):
+        # planners -> MPC -> whole-body tick, one MPC period per CUDA-graph launch, inputs of the period staged on the device
+        cw = wl.PlannerWorkload(B, 9 + rank, change_every=1000, yaw0=0.0, speed=0.5)
+        cin = [[torch.from_numpy(a).to(dev) for a in cw.tick(k)] for k in range(10 * (2 + K))]
+        ctl = BatchedController(B, device=local)
+        for k in range(10):
+            ctl.tick(k, *cin[k])
+        stage = ctl.capture_period()
+
+        def period(p_):
+            for i in range(10):
+                for dst, src in zip(stage, cin[10 * p_ + i]):
+                    dst[i].copy_(src)
+            ctl.replay_period()
+
+        period(1)
+        barrier()
+        e0.record()
+        for p_ in range(2, 2 + K):
+            period(p_)
+        e1.record()
+        barrier()
+        ct = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ct, op=dist.ReduceOp.MAX)
+        aux["control_loop"] = {"value": world * B * 10 * K / (float(ct.item()) * 1e-3), "unit": "control ticks/s", "robots_per_gpu": B,
+                               "ms_per_mpc_period": float(ct.item()) / K, "kernels_per_period": 10 * 5 + 1, "periods": K,
+                               "workload": "BASELINE config 5 at the reference cadence: 10 control ticks (planners + whole-body tick) and one "
+                                           "MPC update solve per robot and period, everything resident in HBM, one CUDA graph per period"}
+        ctl.close()
+
     # ---- roofline of the dominant kernel (the only kernel in a step)
     peaks, which = measured_peaks()
     kern_ms = float(step_ms.mean())

@@ -131,6 +131,14 @@ int qrw_wbctick_run_host(qrw_wbctick_t* h, const double* q, const double* dq, co
 int qrw_wbctick_result_host(qrw_wbctick_t* h, double* tau_ff, double* qdes, double* vdes, double* f_res, double* ddq_cmd);
 int qrw_wbctick_result_device(qrw_wbctick_t* h, const double** tau_ff, const double** qdes, const double** vdes,
                               const double** f_res);
+/* The tick as the control loop calls it (scripts/Controller.py:275-303): q_wbc = (0, 0, h_ref, 0, 0, 0, 1, previous qdes),
+ * b_v = (v_ref[0:6], previous vdes) are built on the device from the handle's own previous outputs; f_cmd is read with a
+ * stride (the MPC result + 12, stride 24 * n_steps = x_f_mpc[12:24, 0], Controller.py:258,300).  set_desired initialises
+ * qdes / vdes (Controller.py:153; host pointers [B][12], NULL = zeros). */
+int qrw_wbctick_set_desired_host(qrw_wbctick_t* h, const double* qdes, const double* vdes);
+int qrw_wbctick_run_ctrl_device(qrw_wbctick_t* h, double h_ref, const double* vref6, const double* f_cmd, int f_stride,
+                                const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                                void* stream);
 /* intermediates handed to QPWBC (Jc [B][216], RNEA [B][6]) and its ddq_res [B][6]; any pointer may be NULL */
 int qrw_wbctick_debug_host(qrw_wbctick_t* h, double* Jc, double* rnea6, double* ddq_res);
 /* diag(crba(q = 0)[:6, :6]): (m, m, m, Ixx, Iyy, Izz) of the whole robot about the base frame */

@@ -268,3 +268,60 @@ int qrw_planner_set_target_host(qrw_planner_t* h, const double* o_target) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- control-loop glue (Controller.py:258-303)
+namespace {
+// q_wbc = (0, 0, h_ref, 0, 0, 0, 1, qdes of the previous tick), b_v = (v_ref[0:6], vdes of the previous tick)
+// (Controller.py:275-283) and f_cmd = x_f_mpc[12:24, 0] (:258, :300) gathered from the MPC result with its stride.
+// Twelve lanes per robot, one per joint / force component.
+__global__ void __launch_bounds__(192) wbc_ctrl_inputs_kernel(const int B, const double h_ref, const double* __restrict__ vref6,
+                                                             const double* __restrict__ f_src, const int f_stride,
+                                                             const double* __restrict__ qdes, const double* __restrict__ vdes,
+                                                             double* __restrict__ q, double* __restrict__ dq, double* __restrict__ f) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t b = t / 12;
+  const int i = (int)(t % 12);
+  if (b >= (size_t)B) return;
+  q[b * 19 + 7 + i] = qdes[b * 12 + i];
+  dq[b * 18 + 6 + i] = vdes[b * 12 + i];
+  f[b * 12 + i] = f_src[b * (size_t)f_stride + i];
+  if (i < 7) q[b * 19 + i] = (i == 2) ? h_ref : (i == 6 ? 1.0 : 0.0);
+  if (i < 6) dq[b * 18 + i] = vref6[b * 6 + i];
+}
+}  // namespace
+
+extern "C" {
+
+// wbc_controller.qdes[7:] / vdes[6:] before the first tick (Controller.py:153: q_init, zeros).  Host pointers [B][12];
+// NULL = zeros.
+int qrw_wbctick_set_desired_host(qrw_wbctick_t* h, const double* qdes, const double* vdes) {
+  if (!h) return fail("qrw_wbctick_set_desired_host: null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  const size_t n = (size_t)h->B * 12 * sizeof(double);
+  if (qdes) CU(cudaMemcpy(h->d_qdes, qdes, n, cudaMemcpyHostToDevice));
+  else CU(cudaMemset(h->d_qdes, 0, n));
+  if (vdes) CU(cudaMemcpy(h->d_vdes, vdes, n, cudaMemcpyHostToDevice));
+  else CU(cudaMemset(h->d_vdes, 0, n));
+  return 0;
+}
+
+// The whole-body tick as scripts/Controller.py:275-303 calls it inside the control loop: the configuration and velocity
+// handed to wbc_controller.compute are built from the PREVIOUS tick's qdes / vdes held by the handle, the reference
+// velocity and the reference height; f_cmd is read with a stride (f_cmd + b * f_stride, e.g. the MPC result + 12 with
+// stride 24 * n_steps).  Device pointers, asynchronous on `stream`.
+int qrw_wbctick_run_ctrl_device(qrw_wbctick_t* h, double h_ref, const double* vref6, const double* f_cmd, int f_stride,
+                                const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                                void* stream) {
+  if (!h || !vref6 || !f_cmd || !contacts || !pgoals || !vgoals || !agoals) return fail("qrw_wbctick_run_ctrl_device: null argument");
+  if (f_stride < 12) return fail("qrw_wbctick_run_ctrl_device: f_stride < 12");
+  CU(cudaSetDevice(h->device));
+  const unsigned grid = (unsigned)((12LL * h->B + 191) / 192);
+  wbc_ctrl_inputs_kernel<<<grid, 192, 0, (cudaStream_t)stream>>>(h->B, h_ref, vref6, f_cmd, f_stride, h->d_qdes, h->d_vdes, h->d_q,
+                                                                h->d_dq, h->d_f);
+  ++g_launches;
+  CU(cudaGetLastError());
+  return qrw_wbctick_run_device(h, h->d_q, h->d_dq, h->d_f, contacts, pgoals, vgoals, agoals, stream);
+}
+
+}  // extern "C"

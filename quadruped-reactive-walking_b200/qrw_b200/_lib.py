@@ -80,6 +80,8 @@ _SIGNATURES = {
     "qrw_wbctick_result_host": (C.c_int, [_vp] * 6),
     "qrw_wbctick_result_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 4),
     "qrw_wbctick_debug_host": (C.c_int, [_vp] * 4),
+    "qrw_wbctick_set_desired_host": (C.c_int, [_vp, _vp, _vp]),
+    "qrw_wbctick_run_ctrl_device": (C.c_int, [_vp, C.c_double, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "qrw_solo12_base_inertia": (C.c_int, [_vp]),
     "qrw_solo12_feet_host": (C.c_int, [C.c_int] + [_vp] * 7),
     "qrw_planner_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,

@@ -297,12 +297,14 @@ class PlannerWorkload:
     changes (joystick codes of Gait::changeGait; 5 = walk).  Deterministic in (B, seed); tick(k) must be called for
     k = 0, 1, 2, ... in order."""
 
-    def __init__(self, B, seed, dt_wbc=0.002, k_mpc=10, codes=(1, 2, 3, 4), change_every=170):
-        self.B, self.dt, self.k_mpc = B, dt_wbc, k_mpc
+    def __init__(self, B, seed, dt_wbc=0.002, k_mpc=10, codes=(1, 2, 3, 4), change_every=170, yaw0=None, speed=1.0):
+        self.B, self.dt, self.k_mpc, self.speed = B, dt_wbc, k_mpc, speed
         self.rng = np.random.default_rng(seed)
         self.codes, self.change_every = tuple(codes), change_every
         self.xy = np.zeros((B, 2))
-        self.yaw = self.rng.uniform(-3.0, 3.0, B)
+        # yaw0 = None: random initial heading (planner-only tests); closed-loop runs through the whole-body tick start at
+        # heading 0, where the feet stand under the shoulders as FootTrajectoryGenerator::initialize assumes
+        self.yaw = self.rng.uniform(-3.0, 3.0, B) if yaw0 is None else np.full(B, float(yaw0))
         self.vref = np.zeros((B, 6))
         self._new_vref()
         self.k = 0
@@ -313,6 +315,7 @@ class PlannerWorkload:
         self.vref[:, 1] = r.uniform(-0.5, 0.5, B)
         self.vref[:, 5] = r.uniform(-0.7, 0.7, B)
         self.vref[r.random(B) < 0.1, 5] = 0.0  # the yaw-rate == 0 branch of the planners
+        self.vref *= self.speed
 
     def tick(self, k):
         assert k == self.k, "ticks must be consumed in order"
@@ -332,7 +335,7 @@ class PlannerWorkload:
         q7[:, 0:2] = self.xy
         q7[:, 2] = r.uniform(0.2, 0.26, B)
         q7[:, 3:7] = euler_to_quaternion(roll, pitch, self.yaw)
-        h_v = self.vref + r.uniform(-0.1, 0.1, (B, 6))
+        h_v = self.vref + self.speed * r.uniform(-0.1, 0.1, (B, 6))
         self.k += 1
         return q7, h_v, self.vref.copy(), code
 
