@@ -363,16 +363,20 @@ def run_b200(args):
 
         period(1)
         barrier()
-        e0.record()
+        pev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
         for p_ in range(2, 2 + K):
+            pev[p_ - 2][0].record()
             period(p_)
-        e1.record()
+            pev[p_ - 2][1].record()
         barrier()
-        ct = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        period_ms = np.array([a.elapsed_time(b) for a, b in pev])
+        ct = torch.tensor([period_ms.sum()], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ct, op=dist.ReduceOp.MAX)
         aux["control_loop"] = {"value": world * B * 10 * K / (float(ct.item()) * 1e-3), "unit": "control ticks/s", "robots_per_gpu": B,
-                               "ms_per_mpc_period": float(ct.item()) / K, "kernels_per_period": 10 * 5 + 1, "periods": K,
+                               "ms_per_mpc_period": float(ct.item()) / K, "period_ms": [round(float(x), 3) for x in period_ms],
+                               "mpc_iters_mean_last_period": float(ctl.mpc.info()["iters"].mean()),
+                               "kernels_per_period": 10 * 5 + 1, "periods": K,
                                "workload": "BASELINE config 5 at the reference cadence: 10 control ticks (planners + whole-body tick) and one "
                                            "MPC update solve per robot and period, everything resident in HBM, one CUDA graph per period"}
         ctl.close()
