@@ -135,3 +135,187 @@ class InvKin:
 
     def get_dq_cmd(self):
         return self._impl.get_dq_cmd().reshape(12, 1).copy()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Planner classes (python/gepadd.cpp:45-175).  The reference wires them by reference: FootstepPlanner and
+# FootTrajectoryGenerator hold a pointer to the Gait object.  Here the Gait object owns a batch-of-one planner handle
+# (qrw_b200.planner.BatchedPlanner) and the other classes attach to it; every method runs the matching stage of the one
+# CUDA kernel.  A StatePlanner built on its own gets its own handle.
+# ------------------------------------------------------------------------------------------------------------------
+def _m34(a):
+    """[1,12] foot-major (3 x 4 column-major) -> 3 x 4 matrix."""
+    return np.asarray(a, dtype=np.float64).reshape(4, 3).T.copy()
+
+
+class _PlannerCore:
+    """Shared batch-of-one planner handle with the last inputs each stage was called with."""
+
+    def __init__(self, dt_mpc, dt_wbc, T_gait, T_mpc, N_gait, k_mpc, h_ref):
+        from qrw_b200.planner import BatchedPlanner
+
+        self.args = dict(dt_mpc=dt_mpc, dt_wbc=dt_wbc, T_gait=T_gait, T_mpc=T_mpc, N_gait=N_gait, k_mpc=k_mpc, h_ref=h_ref)
+        self.impl = BatchedPlanner(1, **self.args)
+        self.cfg = dict(shoulders=None, ftg_target=None, ftg_position=None, max_height=0.05, lock_time=0.07)
+        self.q7 = np.array([[0.0, 0.0, h_ref, 0.0, 0.0, 0.0, 1.0]])
+        self.v6 = np.zeros((1, 6))
+        self.vref6 = np.zeros((1, 6))
+
+    def rebuild(self, **kw):
+        """initialize() of a later class changed a constructor-time constant: new handle, same configuration."""
+        from qrw_b200.planner import BatchedPlanner
+
+        self.args.update(kw)
+        self.impl.close()
+        self.impl = BatchedPlanner(1, **self.args)
+        self.impl.configure(**self.cfg)
+
+    def configure(self, **kw):
+        self.cfg.update(kw)
+        self.impl.configure(**self.cfg)
+
+
+class Gait:
+    """class Gait, python/gepadd.cpp:76-109 (src/Gait.cpp)."""
+
+    def __init__(self):
+        self._core = None
+
+    def initialize(self, dt_in, T_gait_in, T_mpc_in, N_gait):
+        from qrw_b200 import QrwError
+
+        try:
+            # dt_wbc / k_mpc / h_ref are set by the classes that own them (FootstepPlanner / FootTrajectoryGenerator)
+            self._core = _PlannerCore(dt_in, dt_in / 10.0, T_gait_in, T_mpc_in, int(N_gait), 10, 0.0)
+        except QrwError as e:  # Gait.cpp:30-31 throws std::invalid_argument, which Boost.Python maps to ValueError
+            raise ValueError(str(e)) from None
+        self._N = int(N_gait)
+
+    def updateGait(self, k, k_mpc, q, joystickCode):
+        c = self._core
+        if int(k_mpc) != c.args["k_mpc"]:
+            raise ValueError("k_mpc differs from the one the planners were initialised with")
+        c.q7 = np.asarray(q, dtype=np.float64).reshape(-1)[:7][None, :].copy()
+        c.impl.run(int(k), c.q7, c.v6, c.vref6, [int(joystickCode)], stages=1)
+
+    def getCurrentGait(self):
+        return self._core.impl.outputs(("gait",))["gait"].reshape(4, self._N).T.copy()
+
+    def getPastGait(self):
+        return self._core.impl.state()["past"].reshape(4, self._N).T.copy()
+
+    def getDesiredGait(self):
+        return self._core.impl.state()["desired"].reshape(4, self._N).T.copy()
+
+    def isNewPhase(self):
+        return bool(self._core.impl.state()["flags"][0, 0])
+
+    def getIsStatic(self):
+        return bool(self._core.impl.state()["flags"][0, 1])
+
+    def setGait(self, gaitMatrix):  # Gait.cpp:262-269: prints the matrix and returns false
+        print("Gait matrix received by setGait:")
+        print(np.asarray(gaitMatrix))
+        return False
+
+
+class StatePlanner:
+    """class StatePlanner, python/gepadd.cpp:45-73 (src/StatePlanner.cpp)."""
+
+    def __init__(self):
+        self._impl = None
+
+    def initialize(self, dt_in, T_mpc_in, h_ref_in):
+        from qrw_b200.planner import BatchedPlanner
+
+        self._n = int(round(T_mpc_in / dt_in))
+        N = max(self._n + 4, 20)
+        self._impl = BatchedPlanner(1, dt_mpc=dt_in, dt_wbc=dt_in / 10.0, T_gait=T_mpc_in, T_mpc=T_mpc_in, N_gait=N + N % 2, k_mpc=10,
+                                    h_ref=h_ref_in)
+        self._z_warned = False
+
+    def computeReferenceStates(self, q, v, b_vref, z_average):
+        if float(z_average) != 0.0:
+            raise ValueError("z_average != 0 is not supported (the reference always passes 0.0, Controller.py:235-236)")
+        q7 = np.asarray(q, dtype=np.float64).reshape(-1)[:7][None, :]
+        self._impl.run(0, q7, np.asarray(v, np.float64).reshape(1, 6), np.asarray(b_vref, np.float64).reshape(1, 6), None, stages=8)
+
+    def getReferenceStates(self):
+        return self._impl.outputs(("xref",))["xref"].reshape(self._n + 1, 12).T.copy()
+
+    def getNSteps(self):
+        return self._n
+
+
+class FootstepPlanner:
+    """class FootstepPlanner, python/gepadd.cpp:112-141 (src/FootstepPlanner.cpp)."""
+
+    def __init__(self):
+        self._core = None
+
+    def initialize(self, dt_in, dt_wbc_in, T_mpc_in, h_ref_in, shouldersIn, gaitIn, N_gait):
+        c = self._core = gaitIn._core
+        self._N = int(N_gait)
+        sh = np.asarray(shouldersIn, dtype=np.float64)[:3, :4]
+        c.cfg.update(shoulders=sh)
+        c.rebuild(dt_wbc=float(dt_wbc_in), h_ref=float(h_ref_in), k_mpc=int(round(dt_in / dt_wbc_in)))
+
+    def updateFootsteps(self, refresh, k, q, b_v, b_vref):
+        """`k` is the remaining number of control ticks before the next MPC tick and `refresh` the new-MPC-tick flag, as
+        Controller.py:225-227 computes them from the tick index; the kernel takes the tick index itself."""
+        c = self._core
+        k_mpc = c.args["k_mpc"]
+        tick = (k_mpc - int(k)) % k_mpc  # k = k_mpc - tick % k_mpc
+        if bool(refresh) and tick == 0:
+            tick = k_mpc  # any non-zero multiple of k_mpc: refresh = (tick % k_mpc == 0 and tick != 0)
+        elif bool(refresh):
+            raise ValueError("refresh is only meaningful on an MPC tick (k == k_mpc)")
+        c.q7 = np.asarray(q, dtype=np.float64).reshape(-1)[:7][None, :].copy()
+        c.v6 = np.asarray(b_v, dtype=np.float64).reshape(1, 6).copy()
+        c.vref6 = np.asarray(b_vref, dtype=np.float64).reshape(1, 6).copy()
+        c.impl.run(tick, c.q7, c.v6, c.vref6, None, stages=2)
+        return _m34(c.impl.outputs(("o_target",))["o_target"])
+
+    def getFootsteps(self):
+        return self._core.impl.outputs(("fsteps",))["fsteps"].reshape(12, self._N).T.copy()
+
+    def getTargetFootsteps(self):
+        return _m34(self._core.impl.outputs(("o_target",))["o_target"])
+
+    def getRz(self):
+        """Rz as the last statement that wrote it leaves it (FootstepPlanner.cpp:213-214: rotation by the base yaw)."""
+        x, y, z, w = self._core.q7[0, 3:7]
+        yaw = np.arctan2(2 * (x * y + z * w), 1 - 2 * (y * y + z * z))
+        c, s = np.cos(yaw), np.sin(yaw)
+        return np.array([[c, -s, 0.0], [s, c, 0.0], [0.0, 0.0, 1.0]])
+
+
+class FootTrajectoryGenerator:
+    """class FootTrajectoryGenerator, python/gepadd.cpp:144-175 (src/FootTrajectoryGenerator.cpp)."""
+
+    def __init__(self):
+        self._core = None
+
+    def initialize(self, maxHeightIn, lockTimeIn, targetFootstepIn, initialFootPosition, dt_tsid_in, k_mpc_in, gaitIn):
+        c = self._core = gaitIn._core
+        c.cfg.update(ftg_target=np.asarray(targetFootstepIn, np.float64)[:3, :4], ftg_position=np.asarray(initialFootPosition, np.float64)[:3, :4],
+                     max_height=float(maxHeightIn), lock_time=float(lockTimeIn))
+        c.rebuild(dt_wbc=float(dt_tsid_in), k_mpc=int(k_mpc_in))
+
+    def update(self, k, targetFootstep):
+        c = self._core
+        t = np.asarray(targetFootstep, dtype=np.float64)[:3, :4]
+        c.impl.set_target(np.ascontiguousarray(t.T.reshape(1, 12)))
+        c.impl.run(int(k), c.q7, c.v6, c.vref6, None, stages=4)
+
+    def _get(self, name):
+        return _m34(self._core.impl.outputs((name,))[name])
+
+    def getFootPosition(self):
+        return self._get("fpos")
+
+    def getFootVelocity(self):
+        return self._get("fvel")
+
+    def getFootAcceleration(self):
+        return self._get("facc")

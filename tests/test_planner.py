@@ -320,3 +320,39 @@ def test_cuda_planner_rejects_small_gait_matrix():
 
     with pytest.raises(QrwError, match="Increase N_gait"):
         BatchedPlanner(4, N_gait=12)
+
+
+@pytest.mark.gpu
+def test_drop_in_planner_classes_follow_the_controller_call_sequence():
+    """The Boost.Python-shaped classes (libquadruped_reactive_walking.Gait / StatePlanner / FootstepPlanner /
+    FootTrajectoryGenerator) driven exactly as scripts/Controller.py:124-139,222-240 drives them, against the oracle."""
+    import libquadruped_reactive_walking as lqrw
+
+    dt_wbc, dt_mpc, T, N_gait, k_mpc = 0.002, 0.02, 0.32, 20, 10
+    sh = ob.SHOULDERS34.reshape(4, 3).T.copy()
+    sp, gait, fsp, ftg = lqrw.StatePlanner(), lqrw.Gait(), lqrw.FootstepPlanner(), lqrw.FootTrajectoryGenerator()
+    sp.initialize(dt_mpc, T, H_REF)
+    gait.initialize(dt_mpc, T, T, N_gait)
+    fsp.initialize(dt_mpc, dt_wbc, T, H_REF, sh.copy(), gait, N_gait)
+    ftg.initialize(0.05, 0.07, sh.copy(), sh.copy(), dt_wbc, k_mpc, gait)
+    O = ob.OraclePlanner(1, h_ref=H_REF)
+    W = wl.PlannerWorkload(1, 31, codes=(1, 2, 3), change_every=45)
+    for k in range(140):
+        q7, hv, vr, code = W.tick(k)
+        q = np.zeros((19, 1))
+        q[:7, 0] = q7[0]
+        gait.updateGait(k, k_mpc, q[0:7, 0:1], int(code[0]))
+        o_t = fsp.updateFootsteps(k % k_mpc == 0 and k != 0, int(k_mpc - k % k_mpc), q[0:7, 0:1], hv[0].reshape(6, 1).copy(), vr[0])
+        ftg.update(k, o_t)
+        sp.computeReferenceStates(q[0:7, 0:1], hv[0].reshape(6, 1).copy(), vr[0].reshape(6, 1), 0.0)
+        O.run(k, q7, hv, vr, code)
+        o = O.outputs()
+        assert (gait.getCurrentGait() == o["gait"].reshape(4, 20).T).all()
+        assert gait.isNewPhase() == bool(O.state()["flags"][0, 0])
+        assert _close(sp.getReferenceStates(), o["xref"].reshape(17, 12).T)
+        assert _close(fsp.getFootsteps(), o["fsteps"].reshape(12, 20).T)
+        assert _close(o_t, o["o_target"].reshape(4, 3).T)
+        for got, name in ((ftg.getFootPosition(), "fpos"), (ftg.getFootVelocity(), "fvel"), (ftg.getFootAcceleration(), "facc")):
+            assert _close(got, o[name].reshape(4, 3).T), (k, name)
+    with pytest.raises(ValueError):
+        lqrw.Gait().initialize(dt_mpc, T, T, 12)
