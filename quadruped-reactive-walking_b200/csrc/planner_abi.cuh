@@ -15,7 +15,7 @@ constexpr int PLAN_THREADS = 64;  // 16 robots per CTA: the footstep staging (16
 
 // One control tick of the planners of B robots, four lanes per robot (planner_core.cuh).  The footstep matrix of a
 // robot is assembled column by column in shared memory and leaves the SM as one contiguous run per warp (8 robots).
-__global__ void __launch_bounds__(PLAN_THREADS) planner_tick_kernel(const PlanConst C, const PlanMem M, const int k, const int stages,
+__global__ void __launch_bounds__(PLAN_THREADS, 7) planner_tick_kernel(const PlanConst C, const PlanMem M, const int k, const int stages,
                                                                     const double* __restrict__ q7, const double* __restrict__ v6,
                                                                     const double* __restrict__ vref6, const int* __restrict__ code) {
   extern __shared__ __align__(16) double fs_stage[];

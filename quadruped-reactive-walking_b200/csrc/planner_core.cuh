@@ -173,6 +173,15 @@ QRW_HD void quat_to_rpy(const double* q, double rpy[3]) {
   rpy[1] = p;
 }
 
+// sin and cos of one argument in one call (CUDA's sincos shares the argument reduction; same values as sin() / cos())
+QRW_HD void sin_cos(double a, double& s, double& c) {
+#if QRW_ON_GPU
+  sincos(a, &s, &c);
+#else
+  s = sin(a), c = cos(a);
+#endif
+}
+
 // One 5th-order swing polynomial (FootTrajectoryGenerator.cpp:58-71): the reference's closed forms
 QRW_HD void swing_coeffs(double A[6], double a0, double v0, double x0, double xt, double t, double d) {
   const double t2 = t * t, t3 = t2 * t, t4 = t3 * t, t5 = t4 * t, d2 = d * d, d3 = d2 * d, d4 = d3 * d, d5 = d4 * d;
@@ -230,6 +239,13 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
   X.feet_mask = (fl >> 4) & 15;
   X.dirty = 0, X.qstatic_set = 0;
 
+  // yaw (and roll / pitch for xref column 0) of the base, once for all the stages that need it
+  double rpy[3] = {0.0, 0.0, 0.0}, cyaw = 1.0, syaw = 0.0;
+  if (stages & (ST_FOOTSTEPS | ST_STATE | ST_FEETCMD)) {
+    quat_to_rpy(q, rpy);
+    sin_cos(rpy[2], syaw, cyaw);
+  }
+
   // ---- Gait::updateGait (Gait.cpp:189-221)
   if (stages & ST_GAIT) {
     g.is_static = 0;
@@ -261,7 +277,8 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
     }
     if (stance0) {  // :62-73, the stance feet move backwards in the base frame
       const double rot = C.dt_wbc * vref[5];
-      const double c = cos(rot), s = sin(rot);
+      double c, s;
+      sin_cos(rot, s, c);
       const double a = X.cur_fs[0] - C.dt_wbc * vref[0], bb = X.cur_fs[1] - C.dt_wbc * vref[1];
       X.cur_fs[0] = c * a + s * bb;
       X.cur_fs[1] = -s * a + c * bb;
@@ -281,9 +298,11 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
       } else if (!was && is) {
         const double w = vref[5], yaw = w * dt_cum;
         double dx, dy;
+        double c, s;  // yaws(i-1) = w * dt_cum(i-1) is also the argument of dx / dy (:96-111)
+        sin_cos(yaw, s, c);
         if (w != 0) {
-          dx = (hv[0] * sin(w * dt_cum) + hv[1] * (cos(w * dt_cum) - 1.0)) / w;
-          dy = (hv[1] * sin(w * dt_cum) - hv[0] * (cos(w * dt_cum) - 1.0)) / w;
+          dx = (hv[0] * s + hv[1] * (c - 1.0)) / w;
+          dy = (hv[1] * s - hv[0] * (c - 1.0)) / w;
         } else {
           dx = hv[0] * dt_cum, dy = hv[1] * dt_cum;
         }
@@ -296,7 +315,6 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
         ny += hg * (hv[2] * vref[3] - hv[0] * vref[5]);
         nx = dmax(dmin(nx, 0.155), -0.155), ny = dmax(dmin(ny, 0.155), -0.155);
         nx += C.shoulders[3 * j], ny += C.shoulders[3 * j + 1];
-        const double c = cos(yaw), s = sin(yaw);
         v[0] = c * nx - s * ny + dx;
         v[1] = s * nx + c * ny + dy;
         v[2] = 0.0;
@@ -309,9 +327,7 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
     if (first == 0) X.target[0] = fs_col[0], X.target[1] = fs_col[N], X.target[2] = 0.0;
     for (; i < N; ++i) fs_col[i] = 0.0, fs_col[i + N] = 0.0, fs_col[i + 2 * N] = 0.0;
     // computeTargetFootstep (:201-230)
-    double rpy[3];
-    quat_to_rpy(q, rpy);
-    const double c = cos(rpy[2]), s = sin(rpy[2]);
+    const double c = cyaw, s = syaw;
     X.o_target[0] = c * X.target[0] - s * X.target[1] + q[0];
     X.o_target[1] = s * X.target[0] + c * X.target[1] + q[1];
     X.dirty |= ST_FOOTSTEPS;
@@ -383,25 +399,25 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
       double c12[12];
       for (int r = 0; r < 12; ++r) c12[r] = 0.0;
       if (col == 0) {
-        double rpy[3];
-        quat_to_rpy(q, rpy);
         c12[2] = q[2], c12[3] = rpy[0], c12[4] = rpy[1];
         for (int r = 0; r < 6; ++r) c12[6 + r] = hv[r];
       } else {
         const int i = col - 1;
         const double t = (i == C.n_steps - 1) ? C.T_mpc : C.dt_mpc + i * C.lin_step;  // Eigen LinSpaced(n, dt, T_mpc)
         const double w = vref[5];
+        double sw, cw;  // referenceStates_(5, 1+i) = w * t is the argument of every sin / cos of the column
+        sin_cos(w * t, sw, cw);
         if (w != 0) {
-          c12[0] = (vref[0] * sin(w * t) + vref[1] * (cos(w * t) - 1.0)) / w;
-          c12[1] = (vref[1] * sin(w * t) - vref[0] * (cos(w * t) - 1.0)) / w;
+          c12[0] = (vref[0] * sw + vref[1] * (cw - 1.0)) / w;
+          c12[1] = (vref[1] * sw - vref[0] * (cw - 1.0)) / w;
         } else {
           c12[0] = vref[0] * t, c12[1] = vref[1] * t;
         }
         c12[0] += 0.0, c12[1] += 0.0;  // + referenceStates_(0:2, 0), which are set to 0.0 (:27-28)
         c12[2] = C.h_ref + 0.0;
         c12[5] = w * t;
-        c12[6] = vref[0] * cos(c12[5]) - vref[1] * sin(c12[5]);
-        c12[7] = vref[0] * sin(c12[5]) + vref[1] * cos(c12[5]);
+        c12[6] = vref[0] * cw - vref[1] * sw;
+        c12[7] = vref[0] * sw + vref[1] * cw;
         c12[11] = w;
       }
       for (int r = 0; r < 12; ++r) XR[12 * col + r] = c12[r];
@@ -411,9 +427,7 @@ QRW_HD void lane_compute(const PlanConst& C, const PlanMem& M, int b, int j, int
   // ---- feet commands in the base frame (Controller.py:286-296), oRh = Rz(yaw), oTh = (q_x, q_y, 0) (:419-423)
   if (stages & ST_FEETCMD) {
     const double *pc = M.f(F_PCMD, 12, b) + 3 * j, *vc = M.f(F_VCMD, 12, b) + 3 * j;
-    double rpy[3];
-    quat_to_rpy(q, rpy);
-    const double c = cos(rpy[2]), s = sin(rpy[2]);
+    const double c = cyaw, s = syaw;
     const double w[3] = {vref[3], vref[4], vref[5]};
     const double p0[3] = {pc[0], pc[1], pc[2]}, v0[3] = {vc[0], vc[1], vc[2]};
     const double wp[3] = {w[1] * p0[2] - w[2] * p0[1], w[2] * p0[0] - w[0] * p0[2], w[0] * p0[1] - w[1] * p0[0]};
