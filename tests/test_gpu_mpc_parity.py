@@ -172,3 +172,36 @@ def test_full_size_properties():
     X0 = xr.reshape(B, 17, 12)[:, 0]
     vz = X0[:, 8] + 0.02 * (f[:, 0, :, 2].sum(1) / 2.500002861022949 - 9.8100004196167)
     assert np.abs(R[ok, 0, 8] - vz[ok]).max() < 1e-4
+
+
+def test_config3_full_size_mixed_gaits_sampled_against_oracle(oracle):
+    """BASELINE config 3 at its full size: 65,536 instances mixing trot / walk / bounding / pacing / static schedules,
+    cold tick + one update tick.  Instances are independent, so a seeded sample of 192 of them is re-solved by the oracle
+    from the same inputs and history and must match (forces, gait, S_gait, iteration counts); the whole batch must meet
+    the size-independent properties (friction cone, fz bounds, swing forces vanish)."""
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B, S = 65536, 192
+    w = wl.MpcWorkload(B, 2, gaits=wl.GAITS, ticks=3)
+    pick = np.sort(np.random.default_rng(5).choice(B, S, replace=False))
+    gpu, cpu = BatchedMPC(B), oracle.OracleMPC(S)
+    x0 = None
+    for t in range(2):
+        xr, fs = w.inputs(t, x0)
+        gpu.run(t, xr, fs)
+        cpu.run(t, np.ascontiguousarray(xr[pick]), np.ascontiguousarray(fs[pick]), 8)
+        rg, rc = gpu.get_latest_result(), cpu.get_latest_result()
+        assert np.array_equal(gpu.get_gait()[pick], cpu.get_gait()) and np.array_equal(gpu.get_Sgait()[pick], cpu.get_Sgait())
+        assert np.array_equal(gpu.info()["iters"][pick], cpu.info()["iters"]), f"iteration counts, tick {t}"
+        assert_forces_close(rg[pick], rc, f"config 3 sample, tick {t}")
+        info = gpu.info()
+        ok = info["status"] == 1
+        assert ok.mean() > 0.99
+        R = rg.reshape(B, 16, 24)
+        f = R[:, :, 12:].reshape(B, 16, 4, 3)
+        mu = 0.8999999761581421
+        assert (f[ok][..., 2] > -1e-3).all() and (f[ok][..., 2] < 25 + 1e-3).all()
+        assert (np.abs(f[ok][..., 0]) <= mu * f[ok][..., 2] + 1e-3).all() and (np.abs(f[ok][..., 1]) <= mu * f[ok][..., 2] + 1e-3).all()
+        swing = w.gait(t)[:, :16] == 0
+        assert np.abs(f[ok][swing[ok]]).max() < 1e-3
+        x0 = rg[:, :12].copy()
