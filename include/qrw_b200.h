@@ -54,6 +54,9 @@ int qrw_mpc_destroy(qrw_mpc_t* h);
  * the state left by the previous call).  One value for the whole batch. */
 int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const double* d_fsteps, void* stream);
 int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const double* fsteps);
+/* MPC::run with a per-robot call index d_k [B] (device ints): < 0 = robot not called in this launch (solver state and
+ * result untouched), 0 = cold start, > 0 = update path.  For servers whose robots post requests at different times. */
+int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xref, const double* d_fsteps, void* stream);
 /* MPC::get_latest_result(), src/MPC.cpp:604: [B][24*n_steps] */
 int qrw_mpc_result_host(qrw_mpc_t* h, double* out);
 int qrw_mpc_result_device(qrw_mpc_t* h, const double** d_out);
@@ -197,6 +200,26 @@ int qrw_planner_state_host(qrw_planner_t* h, double* past_gait, double* desired_
                            double* t_swing, int* flags);
 /* the `targetFootstep` argument of FootTrajectoryGenerator::update for callers that run stage 4 on its own: [B][12] */
 int qrw_planner_set_target_host(qrw_planner_t* h, const double* o_target);
+
+/* ---------------------------------------------------------------------------------------
+ * MPC server -- the asynchronous mode of scripts/MPC_Wrapper.py (:47-52 shared Values / Arrays, :150-225 the child's
+ * loop, :227-264 the wire format) for B robot processes feeding one GPU.  Slot b of the shared block:
+ *   data_in  [1 + 12 (n+1) + 12 N_gait] doubles = k / k_mpc | xref C order | fsteps C order   (compress_dataIn, :227-243)
+ *   data_out [24 n] doubles, F order                                                            (convert_dataOut, :260-264)
+ *   new_data / new_result: signed chars ('b' Values)
+ * poll = one pass of the child's loop body for every slot that has new data (claimed slots are solved in ONE launch of
+ * the indexed MPC kernel); loop = `while running.value`.  All pointers are host pointers, normally into one shared-memory
+ * block mapped by the robot processes (qrw_b200/mpc_server.py).
+ * ------------------------------------------------------------------------------------- */
+typedef struct qrw_mpc_server qrw_mpc_server_t;
+int qrw_mpc_server_create(qrw_mpc_server_t** out, qrw_mpc_t* mpc);
+int qrw_mpc_server_destroy(qrw_mpc_server_t* s);
+int qrw_mpc_server_slot_doubles(qrw_mpc_server_t* s, int* per_in, int* per_out);
+int qrw_mpc_server_poll_host(qrw_mpc_server_t* s, const double* data_in, signed char* new_data, double* data_out,
+                             signed char* new_result, int* n_served);
+int qrw_mpc_server_loop_host(qrw_mpc_server_t* s, const double* data_in, signed char* new_data, double* data_out,
+                             signed char* new_result, const signed char* running, int idle_us, long long max_rounds,
+                             long long* total_served);
 
 #ifdef __cplusplus
 }

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
                                                            const int sms, const double* __restrict__ xref,
                                                            const double* __restrict__ fsteps, double* st_d,
                                                            int* st_i, double* out, int* info, double* rho,
-                                                           double* dbg, int* counter) {
+                                                           double* dbg, int* counter, const int* __restrict__ k_arr) {
   extern __shared__ __align__(16) double slab[];
   int* next = reinterpret_cast<int*>(slab + v2::V_INT) + 127;
   const int recw = (blockIdx.x / sms) & 3;
@@ -102,8 +102,17 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
     __syncthreads();
     const int b = *next;
     if (b >= B) break;
+    int f = first;
+    if (k_arr) {  // per-instance call index (qrw_mpc_run_indexed_device): < 0 = no call for this robot in this launch
+      const int kb = k_arr[b];
+      if (kb < 0) {
+        __syncthreads();
+        continue;
+      }
+      f = kb == 0 ? 1 : 0;
+    }
     v2::mpc_v2_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
-                     st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                     st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, f,
                      out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw);
     __syncthreads();
   }
@@ -576,7 +585,7 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
     if (grid > h->B) grid = h->B;
     mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, h->sms, d_xref, d_fsteps,
                                                           h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
-                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr);
   } else if (h->variant == 1) {
     int grid = 2 * h->sms;  // two 84 KB slabs (16 warps) per SM
     if (grid > h->B) grid = h->B;
@@ -591,6 +600,24 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
                                                       h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
                                                       h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
   }
+  ++g_launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+// MPC::run with a PER-ROBOT call index: d_k[b] < 0 -> robot b is not called in this launch (its solver state and its
+// result stay as they are), 0 -> cold start (create_matrices / osqp_setup path), > 0 -> update path.  This is what a
+// server needs when robots post their MPC requests at different times (qrw_b200/mpc_server.py).
+int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xref, const double* d_fsteps, void* stream) {
+  if (!h || !d_k || !d_xref || !d_fsteps) return fail("qrw_mpc_run_indexed_device: null argument");
+  if (h->variant != 2) return fail("qrw_mpc_run_indexed_device: only the default kernel (variant 2) takes a per-robot index");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
+  int grid = 2 * h->sms;
+  if (grid > h->B) grid = h->B;
+  mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
+                                                        h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k);
   ++g_launches;
   CU(cudaGetLastError());
   return 0;
@@ -1018,3 +1045,5 @@ int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, doubl
 
 }  // extern "C"
 #include "planner_abi.cuh"
+#include <time.h>
+#include "transport_abi.cuh"

@@ -52,6 +52,12 @@ _SIGNATURES = {
     "qrw_mpc_destroy": (C.c_int, [_vp]),
     "qrw_mpc_run_device": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
     "qrw_mpc_run_host": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "qrw_mpc_run_indexed_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "qrw_mpc_server_create": (C.c_int, [C.POINTER(_vp), _vp]),
+    "qrw_mpc_server_destroy": (C.c_int, [_vp]),
+    "qrw_mpc_server_slot_doubles": (C.c_int, [_vp, _ip, _ip]),
+    "qrw_mpc_server_poll_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _ip]),
+    "qrw_mpc_server_loop_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_longlong, C.POINTER(C.c_longlong)]),
     "qrw_mpc_result_host": (C.c_int, [_vp, _vp]),
     "qrw_mpc_result_device": (C.c_int, [_vp, C.POINTER(_vp)]),
     "qrw_mpc_gait_host": (C.c_int, [_vp, _vp]),
