@@ -6,7 +6,7 @@ TAG=${1:-run}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi.txt 2>&1
-timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/rc.txt
+timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/rc.txt
 tail -3 $OUT/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $OUT/rc.txt
 timeout 900 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?" | tee -a $OUT/rc.txt
@@ -22,4 +22,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:mpc_
 echo "ncu mpc rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"wbc_tick_pre_kernel|wbc_solve_kernel|wbc_tick_post_kernel" -s 9 -c 3 -f -o $OUT/prof_wbc $SMALL > $OUT/ncu_wbc.log 2>&1
 echo "ncu wbc rc=$?" | tee -a $OUT/rc.txt
+ls -la $OUT
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:planner_tick_kernel -s 10 -c 2 -f -o $OUT/prof_planner $SMALL > $OUT/ncu_planner.log 2>&1
+echo "ncu planner rc=$?" | tee -a $OUT/rc.txt
+for r in prof_mpc prof_wbc prof_planner; do ncu -i $OUT/$r.ncu-rep --page raw --csv > $OUT/${r}_raw.csv 2>/dev/null; done
 ls -la $OUT
