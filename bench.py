@@ -58,6 +58,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = 48 per host thread)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--work-order", type=int, default=0, choices=[0, 1],
+                    help="0 (default): the persistent MPC grid takes robots in index order; 1: longest-expected-solve first (A/B)")
     ap.add_argument("--wbc-batch", type=int, default=65536, help="robots in the whole-body-tick leg (BASELINE config 4); 0 skips it")
     return ap.parse_args()
 
@@ -191,6 +193,7 @@ def run_b200(args):
     # ---- pre-pass (untimed): closed-loop inputs of ticks 1..T, state snapshot after tick 0
     w = wl.MpcWorkload(B, 1 + rank, gaits=("trot",), ticks=T + 2)
     mpc = BatchedMPC(B, device=local)
+    mpc.set_work_order(args.work_order)
     pin_x, pin_f, pin_r = mpc.pinned()
     xr, fs = w.inputs(0)
     mpc.run(0, xr, fs)

@@ -75,6 +75,10 @@ int qrw_mpc_debug_host(qrw_mpc_t* h, double* out /* [B][1281] */);
  * 0 = one warp per instance (mpc_core.cuh, the round-1 v0 kernel kept for A/B checks).  Both carry the
  * same persistent state and follow the same OSQP iterate sequence. */
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant);
+/* work order of the persistent grid (default kernel): 0 (default) = index order; 1 = robots sorted by the ADMM iteration
+ * count of their previous solve, longest first (measured on B200: no gain, kept as an A/B hook).  Results do not depend
+ * on it. */
+int qrw_mpc_set_work_order(qrw_mpc_t* h, int longest_first);
 /* The solver state carried from call to call (scaled ADMM iterates, rho, stale B_k values, gait,
  * S_gait -- the reference keeps it inside OSQP's workspace and the MPC object).  Snapshot and
  * restore, e.g. to replay a benchmark from the same history or to checkpoint a fleet. */

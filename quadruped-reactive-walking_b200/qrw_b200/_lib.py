@@ -66,6 +66,7 @@ _SIGNATURES = {
     "qrw_mpc_set_max_iter": (C.c_int, [_vp, C.c_int]),
     "qrw_mpc_debug_host": (C.c_int, [_vp, _vp]),
     "qrw_mpc_set_kernel": (C.c_int, [_vp, C.c_int]),
+    "qrw_mpc_set_work_order": (C.c_int, [_vp, C.c_int]),
     "qrw_mpc_state_bytes": (C.c_int, [_vp, C.POINTER(C.c_size_t)]),
     "qrw_mpc_state_save": (C.c_int, [_vp, _vp, _vp]),
     "qrw_mpc_state_load": (C.c_int, [_vp, _vp, _vp]),

@@ -132,6 +132,10 @@ class BatchedMPC:
         """1 = CTA per instance (default), 0 = warp per instance (v0)."""
         check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
 
+    def set_work_order(self, longest_first):
+        """False (default): the persistent grid takes robots in index order; True: longest-expected-solve first."""
+        check(self._L.qrw_mpc_set_work_order(self._h, int(bool(longest_first))))
+
     def enable_debug(self):
         check(self._L.qrw_mpc_debug_host(self._h, None))
 
