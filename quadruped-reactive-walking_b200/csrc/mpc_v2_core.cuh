@@ -434,6 +434,9 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
 QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, const double* fs, double* st_d,
                          int* st_i, int first, double* out, int* info, double* rho_out, double* dbg, int recw) {
   const Sm S(slab);
+#ifdef QRW_V2_TIMING
+  const long long t_entry = clock64();
+#endif
   const int tid = cta::tid();
   const int k = tid >> 4, j = tid & 15, w = tid >> 5, l = tid & 31;
   const int NG = C.N_gait;
@@ -701,12 +704,33 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   int n_factor = 0;
   bool refactor = true;
 
+#ifdef QRW_V2_TIMING
+  // probe build (tools/timing_probe.py, -DQRW_V2_TIMING): cycles of the segments of an iteration seen by thread 0 of a warp
+  // that does NOT run the chain (0: phases 1-4, 3: phases 5-7), by lane 0 of the chain warp (4: the chain), and per solve
+  // (5: everything before the loop, 6: factorisations, 7: residual checks).  Parked in the last entries of the debug dump.
+  long long tq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const int tw = ((recw + 1) & 7) * 32;
+  tq[5] = clock64() - t_entry;
+#define QRW_TICK(i, t0) tq[i] += clock64() - (t0)
+#else
+#define QRW_TICK(i, t0) ((void)0)
+#endif
   // ---- ADMM (osqp_solve)
   int status = ST_UNSOLVED;
   int iter = 0;
   for (iter = 1; iter <= C.max_iter; ++iter) {
+#ifdef QRW_V2_TIMING
+    long long tA = clock64();
+#endif
     if (refactor) {
+#ifdef QRW_V2_TIMING
+      const long long tF = clock64();
+#endif
       factor(C, S, R, Rh, S.red[120], tid);
+      QRW_TICK(6, tF);
+#ifdef QRW_V2_TIMING
+      tA = clock64();
+#endif
       ++n_factor;
       refactor = false;
     }
@@ -775,11 +799,21 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       if (j >= 6) v += C.dt * BAk[j - 6];
       rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
     }
+    QRW_TICK(0, tA);
     cta::bar();
+#ifdef QRW_V2_TIMING
+    tA = clock64();
+#endif
     // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
     // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
     if (w == recw) state_recurrence(S.Sig, S.T, S.rec, l);
+#ifdef QRW_V2_TIMING
+    if (w == recw) QRW_TICK(4, tA);
+#endif
     cta::bar();
+#ifdef QRW_V2_TIMING
+    tA = clock64();
+#endif
     // (5) dynamics rows applied to the new states: r = E (-D_X x~_X + A D_X x~_X^{k-1})
     double xtX = 0.0, rX = 0.0;
     if (isv) {
@@ -841,8 +875,12 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         R.zB = znc;
       }
     }
+    QRW_TICK(3, tA);
     if (iter % C.check_every == 0) {
       // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
+#ifdef QRW_V2_TIMING
+      const long long tC = clock64();
+#endif
       cta::bar();  // everyone is done with the exchange buffers of this iteration
       double yA = 0.0, yB = 0.0;
       if (isv) {
@@ -949,11 +987,22 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         }
       }
       cta::bar();
+      QRW_TICK(7, tC);
     }
   }
   if (iter > C.max_iter) iter = C.max_iter;
   if (status == ST_UNSOLVED) status = ST_MAX_ITER;
 
+#ifdef QRW_V2_TIMING
+  if (dbg) {
+    if (tid == tw) {
+      dbg[1272] = (double)tq[0], dbg[1275] = (double)tq[3];
+      for (int i = 5; i < 8; ++i) dbg[1273 + i] = (double)tq[i];
+    }
+    if (w == recw && l == 0) dbg[1276] = (double)tq[4];
+    if (tid == 0) dbg[1277] = (double)(iter > C.max_iter ? C.max_iter : iter);
+  }
+#endif
   // ---- retrieve_result (MPC.cpp:569-599) + state carried to the next call
   cta::bar();
   const bool bad = (status == ST_NON_CVX);
