@@ -74,12 +74,11 @@ struct Sm {
 QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
 
 // per-thread registers of variable lane j = 3 foot + axis of stage k (lanes 12..15 of a stage idle):
-//   bc[0..2] = B_k(9..11, j); row j of F_k^-1 and GF live in the record (R_FI, R_GF)
+//   row j of F_k^-1 and GF and column j of B_k live in the record (R_FI, R_GF, R_BANG)
 //   xf, xX: scaled iterates of f_k[j], X_{k+1}[j]; z1, y1, e1: dynamics row (k,j); y2: force-enable row (k,j)
 //   friction-cone rows of the foot, two slots: axis x -> rows 0,1 (+-fx - mu fz), axis y -> rows 2,3, axis z -> row 4 (-fz)
 //   in slot A and nothing in slot B
 struct Regs {
-  double bc[3];
   double xf, xX, dF, dX, z1, y1, e1, y2;
   double zA, yA, eA, zB, yB, eB;
 };
@@ -118,7 +117,8 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
   double* N = rec + R_N;
   double* W = S.W;
   double F[12];
-  const double b0 = R.bc[0], b1 = R.bc[1], b2 = R.bc[2];
+  // B_k(9..11, j) from the stage record (kept in registers across the ADMM loop they cost six registers for nothing)
+  const double b0 = isv ? Bk[j] : 0.0, b1 = isv ? Bk[12 + j] : 0.0, b2 = isv ? Bk[24 + j] : 0.0;
   // ---- (a) row j of F_k
   if (isv) {
     const double e6 = Ek[6 + c3], e9 = Ek[9], e10 = Ek[10], e11 = Ek[11];
@@ -462,7 +462,6 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   for (int i = tid; i < 576; i += NT) S.rec[SR * (i / 36) + R_BANG + (i % 36)] = first ? 0.0 : st_d[ST_BANG + i];
   if (tid < 32) gait[tid] = first ? 0 : st_i[tid];
   if (tid < NS) sb[tid] = first ? 0 : st_i[32 + tid];
-  R.bc[0] = R.bc[1] = R.bc[2] = 0.0;
   R.xf = R.xX = R.z1 = R.y1 = R.y2 = R.zA = R.yA = R.zB = R.yB = 0.0;
   if (!first && isv) {
     R.xf = st_d[ST_X + gvar(k, j)];
@@ -587,11 +586,8 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     if (hasB) Ek[rowA + 1] = 1.0;
   }
   cta::bar();
-  if (isv) {
-    R.bc[0] = Bk[j];
-    R.bc[1] = Bk[12 + j];
-    R.bc[2] = Bk[24 + j];
-  }
+  double bc0 = 0.0, bc1 = 0.0, bc2 = 0.0;  // B_k(9..11, j), live during the Ruiz passes only
+  if (isv) bc0 = Bk[j], bc1 = Bk[12 + j], bc2 = Bk[24 + j];
   const int bit = isv ? ((sb[k] >> ft) & 1) : 0;
 
   // ---- Ruiz equilibration, 10 passes (OSQP scale_data; rerun on every call, MPC.cpp:541,548)
@@ -604,9 +600,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       const double d = R.dF;
       double nrm = cscale * C.wf * d * d;
       nrm = dmax(nrm, C.dtm * Ek[6 + c3] * d);
-      nrm = dmax(nrm, fabs(R.bc[0]) * Ek[9] * d);
-      nrm = dmax(nrm, fabs(R.bc[1]) * Ek[10] * d);
-      nrm = dmax(nrm, fabs(R.bc[2]) * Ek[11] * d);
+      nrm = dmax(nrm, fabs(bc0) * Ek[9] * d);
+      nrm = dmax(nrm, fabs(bc1) * Ek[10] * d);
+      nrm = dmax(nrm, fabs(bc2) * Ek[11] * d);
       if (bit) nrm = dmax(nrm, e2 * d);
       const double* Ec = Ek + 24 + 5 * ft;
       if (c3 < 2) {
@@ -709,6 +705,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   // that does NOT run the chain (0: phases 1-4, 3: phases 5-7), by lane 0 of the chain warp (4: the chain), and per solve
   // (5: everything before the loop, 6: factorisations, 7: residual checks).  Parked in the last entries of the debug dump.
   long long tq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long tp[7] = {0, 0, 0, 0, 0, 0, 0};  // phases (1)..(7) one by one
   const int tw = ((recw + 1) & 7) * 32;
   tq[5] = clock64() - t_entry;
 #define QRW_TICK(i, t0) tq[i] += clock64() - (t0)
@@ -718,9 +715,11 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   // ---- ADMM (osqp_solve)
   int status = ST_UNSOLVED;
   int iter = 0;
+  int until_check = C.check_every;  // countdown instead of iter % check_every (an integer division per iteration)
   for (iter = 1; iter <= C.max_iter; ++iter) {
 #ifdef QRW_V2_TIMING
     long long tA = clock64();
+    long long tL = tA;
 #endif
     if (refactor) {
 #ifdef QRW_V2_TIMING
@@ -730,6 +729,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       QRW_TICK(6, tF);
 #ifdef QRW_V2_TIMING
       tA = clock64();
+      tL = tA;
 #endif
       ++n_factor;
       refactor = false;
@@ -746,6 +746,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       BDk[j] = uA + uB;
     }
     cta::wsync();
+#ifdef QRW_V2_TIMING
+    tp[0] += clock64() - tL, tL = clock64();
+#endif
     // (2) t_f = sigma x_f + D_f (A' u)_f
     if (isv) {
       double v = C.dtm * BAk[6 + c3];
@@ -760,6 +763,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       BBk[j] = C.sigma * R.xf + R.dF * v;
     }
     cta::wsync();
+#ifdef QRW_V2_TIMING
+    tp[1] += clock64() - tL, tL = clock64();
+#endif
     // (3) u_f = F^-1 t_f and w = GF t_f (rows 6..11) from the same broadcast of t_f;
     //     m = u - rho E w: what the state system sees of the dynamics rows; A_k = sigma x_X - D_X m_k
     double uf = 0.0, wv = 0.0, mk = 0.0;
@@ -793,6 +799,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       rec[R_A + j] = C.sigma * R.xX - R.dX * mk;
     }
     cta::wsync();
+#ifdef QRW_V2_TIMING
+    tp[2] += clock64() - tL, tL = clock64();
+#endif
     // (4) CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
     if (isv && k > 0) {
       double v = mk;
@@ -800,6 +809,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
     }
     QRW_TICK(0, tA);
+#ifdef QRW_V2_TIMING
+    tp[3] += clock64() - tL;
+#endif
     cta::bar();
 #ifdef QRW_V2_TIMING
     tA = clock64();
@@ -813,6 +825,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     cta::bar();
 #ifdef QRW_V2_TIMING
     tA = clock64();
+    tL = tA;
 #endif
     // (5) dynamics rows applied to the new states: r = E (-D_X x~_X + A D_X x~_X^{k-1})
     double xtX = 0.0, rX = 0.0;
@@ -827,6 +840,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       BAk[j] = rX;
     }
     cta::wsync();
+#ifdef QRW_V2_TIMING
+    tp[4] += clock64() - tL, tL = clock64();
+#endif
     // (6) x~_f = u_f - rho GF' r ;  z~ (dynamics rows) = r + w - rho M r
     double xtf = 0.0, zt = rX;
     if (isv) {
@@ -842,6 +858,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       }
     }
     cta::wsync();
+#ifdef QRW_V2_TIMING
+    tp[5] += clock64() - tL, tL = clock64();
+#endif
     // (7) relaxation, projection, dual update, x update
     if (isv) {
       const double zr = C.alpha * zt + (1.0 - C.alpha) * R.z1;
@@ -876,7 +895,11 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       }
     }
     QRW_TICK(3, tA);
-    if (iter % C.check_every == 0) {
+#ifdef QRW_V2_TIMING
+    tp[6] += clock64() - tL;
+#endif
+    if (--until_check == 0) {
+      until_check = C.check_every;
       // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
 #ifdef QRW_V2_TIMING
       const long long tC = clock64();
@@ -998,6 +1021,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     if (tid == tw) {
       dbg[1272] = (double)tq[0], dbg[1275] = (double)tq[3];
       for (int i = 5; i < 8; ++i) dbg[1273 + i] = (double)tq[i];
+      for (int i = 0; i < 7; ++i) dbg[1260 + i] = (double)tp[i];
     }
     if (w == recw && l == 0) dbg[1276] = (double)tq[4];
     if (tid == 0) dbg[1277] = (double)(iter > C.max_iter ? C.max_iter : iter);

@@ -19,6 +19,8 @@ for B in (148, 296, 4096):
     xr, fs = w.inputs(1, x0)
     m.run(1, xr, fs)
     d = m.debug()["bounds"]  # last 192 entries of the dump; the probe build parks its counters at [183:189]
+    ph = d[:, 171:178] / d[:, 188][:, None]
+    print(f"B={B:5d}: cycles per iteration by phase (1)..(7): " + " ".join(f"{x:6.0f}" for x in ph.mean(0)))
     t = d[:, 183:192]
     it = t[:, 5]
     per = t[:, :5] / it[:, None]
