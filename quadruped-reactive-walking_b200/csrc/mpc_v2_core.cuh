@@ -449,7 +449,13 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   // friction-cone rows owned by this lane (stage-local row index; slot B only for the x and y axes)
   const int rowA = 24 + 5 * ft + (c3 < 2 ? 2 * c3 : 4);
   const bool hasB = isv && c3 < 2;
-  double* rec = S.rec + SR * k;
+  int rec_off = SR * k;
+#if QRW_ON_GPU
+  // opaque to the compiler: otherwise ptxas re-derives the record address from threadIdx (S2R + 4 integer ops, ~45 cycles
+  // of latency) at the head of every phase of the ADMM loop instead of keeping one register live (SASS of r01b)
+  asm volatile("" : "+r"(rec_off));
+#endif
+  double* rec = S.rec + rec_off;
   double* BAk = rec + R_BA;
   double* BBk = rec + R_BB;
   double* BCk = rec + R_BC;
