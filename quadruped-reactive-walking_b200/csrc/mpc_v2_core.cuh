@@ -29,6 +29,15 @@
 namespace qrw {
 namespace v2 {
 
+#ifdef QRW_V2_TIMING
+// clock read that the compiler may not move across barriers or shared-memory traffic (probe build only)
+__device__ __forceinline__ long long qrw_clock() {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+  return t;
+}
+#endif
+
 constexpr int NT = 256;  // threads per CTA
 constexpr int LD = 14;   // padded row length of the 12x12 matrices in shared memory (conflict-free LDS.128)
 constexpr int MS = 12 * LD;
@@ -345,6 +354,18 @@ QRW_HD double dot12(const double* m, const double* v) {
   }
   return (a0 + a1) + (a2 + a3);
 }
+// same product with the four partial sums accumulated in ascending order (the order phase (3) has always used)
+QRW_HD double dot12a(const double* m, const double* v) {
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+  for (int b = 0; b < 12; b += 4) {
+    a0 += m[b] * v[b];
+    a1 += m[b + 1] * v[b + 1];
+    a2 += m[b + 2] * v[b + 2];
+    a3 += m[b + 3] * v[b + 3];
+  }
+  return (a0 + a1) + (a2 + a3);
+}
 QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, int lane) {
   const int i0 = lane & 15;
   const bool up = lane >= 16;
@@ -435,7 +456,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
                          int* st_i, int first, double* out, int* info, double* rho_out, double* dbg, int recw) {
   const Sm S(slab);
 #ifdef QRW_V2_TIMING
-  const long long t_entry = clock64();
+  const long long t_entry = qrw_clock();
 #endif
   const int tid = cta::tid();
   const int k = tid >> 4, j = tid & 15, w = tid >> 5, l = tid & 31;
@@ -713,8 +734,8 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   long long tq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tp[7] = {0, 0, 0, 0, 0, 0, 0};  // phases (1)..(7) one by one
   const int tw = ((recw + 1) & 7) * 32;
-  tq[5] = clock64() - t_entry;
-#define QRW_TICK(i, t0) tq[i] += clock64() - (t0)
+  tq[5] = qrw_clock() - t_entry;
+#define QRW_TICK(i, t0) tq[i] += qrw_clock() - (t0)
 #else
 #define QRW_TICK(i, t0) ((void)0)
 #endif
@@ -724,17 +745,17 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   int until_check = C.check_every;  // countdown instead of iter % check_every (an integer division per iteration)
   for (iter = 1; iter <= C.max_iter; ++iter) {
 #ifdef QRW_V2_TIMING
-    long long tA = clock64();
+    long long tA = qrw_clock();
     long long tL = tA;
 #endif
     if (refactor) {
 #ifdef QRW_V2_TIMING
-      const long long tF = clock64();
+      const long long tF = qrw_clock();
 #endif
       factor(C, S, R, Rh, S.red[120], tid);
       QRW_TICK(6, tF);
 #ifdef QRW_V2_TIMING
-      tA = clock64();
+      tA = qrw_clock();
       tL = tA;
 #endif
       ++n_factor;
@@ -753,7 +774,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING
-    tp[0] += clock64() - tL, tL = clock64();
+    tp[0] += qrw_clock() - tL, tL = qrw_clock();
 #endif
     // (2) t_f = sigma x_f + D_f (A' u)_f
     if (isv) {
@@ -770,35 +791,22 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING
-    tp[1] += clock64() - tL, tL = clock64();
+    tp[1] += qrw_clock() - tL, tL = qrw_clock();
 #endif
     // (3) u_f = F^-1 t_f and w = GF t_f (rows 6..11) from the same broadcast of t_f;
     //     m = u - rho E w: what the state system sees of the dynamics rows; A_k = sigma x_X - D_X m_k
     double uf = 0.0, wv = 0.0, mk = 0.0;
     if (isv) {
-      double tv[12];
+      // rows of F^-1 and GF as six LDS.128 each, issued back to back with the broadcast of t_f: left to itself ptxas
+      // loaded them one LDS.64 at a time right in front of the FMA that uses it (a shared-memory latency per product)
+      double tv[12], fv[12];
       cta::lds12(BBk, tv);
-      const double* fi = rec + R_FI + LD * j;
-      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll
-      for (int b = 0; b < 12; b += 4) {
-        a0 += fi[b] * tv[b];
-        a1 += fi[b + 1] * tv[b + 1];
-        a2 += fi[b + 2] * tv[b + 2];
-        a3 += fi[b + 3] * tv[b + 3];
-      }
-      uf = (a0 + a1) + (a2 + a3);
+      cta::lds12(rec + R_FI + LD * j, fv);  // (no warp fence here: lanes 12..15 of a stage are not in this branch)
+      uf = dot12a(fv, tv);
       if (j >= 6) {
-        const double* g = rec + R_GF + LD * (j - 6);
-        double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
-#pragma unroll
-        for (int b = 0; b < 12; b += 4) {
-          b0 += g[b] * tv[b];
-          b1 += g[b + 1] * tv[b + 1];
-          b2 += g[b + 2] * tv[b + 2];
-          b3 += g[b + 3] * tv[b + 3];
-        }
-        wv = (b0 + b1) + (b2 + b3);
+        double gv[12];
+        cta::lds12(rec + R_GF + LD * (j - 6), gv);
+        wv = dot12a(gv, tv);
       }
       mk = u1 - Rh.rho_eq * (R.e1 * wv);
       BAk[j] = mk;
@@ -806,7 +814,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING
-    tp[2] += clock64() - tL, tL = clock64();
+    tp[2] += qrw_clock() - tL, tL = qrw_clock();
 #endif
     // (4) CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
     if (isv && k > 0) {
@@ -816,11 +824,11 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     QRW_TICK(0, tA);
 #ifdef QRW_V2_TIMING
-    tp[3] += clock64() - tL;
+    tp[3] += qrw_clock() - tL;
 #endif
     cta::bar();
 #ifdef QRW_V2_TIMING
-    tA = clock64();
+    tA = qrw_clock();
 #endif
     // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
     // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
@@ -830,7 +838,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
 #endif
     cta::bar();
 #ifdef QRW_V2_TIMING
-    tA = clock64();
+    tA = qrw_clock();
     tL = tA;
 #endif
     // (5) dynamics rows applied to the new states: r = E (-D_X x~_X + A D_X x~_X^{k-1})
@@ -847,7 +855,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING
-    tp[4] += clock64() - tL, tL = clock64();
+    tp[4] += qrw_clock() - tL, tL = qrw_clock();
 #endif
     // (6) x~_f = u_f - rho GF' r ;  z~ (dynamics rows) = r + w - rho M r
     double xtf = 0.0, zt = rX;
@@ -865,7 +873,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING
-    tp[5] += clock64() - tL, tL = clock64();
+    tp[5] += qrw_clock() - tL, tL = qrw_clock();
 #endif
     // (7) relaxation, projection, dual update, x update
     if (isv) {
@@ -902,13 +910,13 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     }
     QRW_TICK(3, tA);
 #ifdef QRW_V2_TIMING
-    tp[6] += clock64() - tL;
+    tp[6] += qrw_clock() - tL;
 #endif
     if (--until_check == 0) {
       until_check = C.check_every;
       // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
 #ifdef QRW_V2_TIMING
-      const long long tC = clock64();
+      const long long tC = qrw_clock();
 #endif
       cta::bar();  // everyone is done with the exchange buffers of this iteration
       double yA = 0.0, yB = 0.0;
