@@ -802,12 +802,11 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       double tv[12], fv[12];
       cta::lds12(BBk, tv);
       cta::lds12(rec + R_FI + LD * j, fv);  // (no warp fence here: lanes 12..15 of a stage are not in this branch)
+      double gv[12];  // lanes j < 6 have no GF row: they read the (valid, aligned) words in front of it and drop the product
+      cta::lds12(rec + R_GF + LD * (j - 6), gv);
       uf = dot12a(fv, tv);
-      if (j >= 6) {
-        double gv[12];
-        cta::lds12(rec + R_GF + LD * (j - 6), gv);
-        wv = dot12a(gv, tv);
-      }
+      const double wq = dot12a(gv, tv);
+      if (j >= 6) wv = wq;
       mk = u1 - Rh.rho_eq * (R.e1 * wv);
       BAk[j] = mk;
       rec[R_A + j] = C.sigma * R.xX - R.dX * mk;
@@ -860,16 +859,19 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     // (6) x~_f = u_f - rho GF' r ;  z~ (dynamics rows) = r + w - rho M r
     double xtf = 0.0, zt = rX;
     if (isv) {
-      const double r0 = BAk[6], r1 = BAk[7], r2 = BAk[8], r3 = BAk[9], r4 = BAk[10], r5 = BAk[11];
+      // everything the phase reads is requested first (three LDS.128 for r, six LDS.64 for the GF column, three
+      // LDS.128 for the M row); lanes j < 6 have no M row: they read the (valid, aligned) words in front of it and drop them
+      double r[6], mr[6], gcv[6];
+      cta::lds6(BAk + 6, r);
       const double* gc = rec + R_GF + j;  // column j of GF
-      const double s0 = (gc[0] * r0 + gc[LD] * r1) + (gc[2 * LD] * r2 + gc[3 * LD] * r3) + (gc[4 * LD] * r4 + gc[5 * LD] * r5);
+#pragma unroll
+      for (int q = 0; q < 6; ++q) gcv[q] = gc[q * LD];
+      cta::lds6(rec + R_MR + 6 * (j - 6), mr);
+      const double s0 = (gcv[0] * r[0] + gcv[1] * r[1]) + (gcv[2] * r[2] + gcv[3] * r[3]) + (gcv[4] * r[4] + gcv[5] * r[5]);
       xtf = uf - Rh.rho_eq * s0;
       BCk[j] = R.dF * xtf;
-      if (j >= 6) {
-        const double* Mr = rec + R_MR + 6 * (j - 6);
-        const double s1 = (Mr[0] * r0 + Mr[1] * r1) + (Mr[2] * r2 + Mr[3] * r3) + (Mr[4] * r4 + Mr[5] * r5);
-        zt = rX + (wv - Rh.rho_eq * s1);
-      }
+      const double s1 = (mr[0] * r[0] + mr[1] * r[1]) + (mr[2] * r[2] + mr[3] * r[3]) + (mr[4] * r[4] + mr[5] * r[5]);
+      if (j >= 6) zt = rX + (wv - Rh.rho_eq * s1);
     }
     cta::wsync();
 #ifdef QRW_V2_TIMING

@@ -92,6 +92,13 @@ __device__ __forceinline__ void lds12(const double* p, double* v) {
   for (int i = 0; i < 12; i += 2)
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
 }
+// v[0..5] = p[0..5] (16-byte aligned) as three LDS.128 issued back to back
+__device__ __forceinline__ void lds6(const double* p, double* v) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+#pragma unroll
+  for (int i = 0; i < 6; i += 2)
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
+}
 // Scheduling fence for ptxas: a warp barrier is never crossed by its instruction scheduler, so the loads issued
 // before it stay grouped ahead of the arithmetic that follows (costs one issue slot).
 __device__ __forceinline__ void sched_fence() { __syncwarp(); }
@@ -112,6 +119,9 @@ double shfl_xor(double v, int m);
 inline void sched_fence() {}
 inline void lds12(const double* p, double* v) {
   for (int i = 0; i < 12; ++i) v[i] = p[i];
+}
+inline void lds6(const double* p, double* v) {
+  for (int i = 0; i < 6; ++i) v[i] = p[i];
 }
 }  // namespace cta
 }  // namespace qrw
