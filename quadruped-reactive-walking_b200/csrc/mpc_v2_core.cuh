@@ -366,86 +366,152 @@ QRW_HD double dot12a(const double* m, const double* v) {
   }
   return (a0 + a1) + (a2 + a3);
 }
+// Scheduling (v2.7): a step is one dependent sequence  STS -> LDS.128 x6 (the broadcast) -> 3 DFMA deep -> 3 DADD -> STS.
+// Shared memory serves a warp's requests in order, so every load issued between the store and the broadcast loads of
+// the next step delays that step: the matrix column / row of step t+1 is therefore requested in step t, right behind
+// the broadcast loads (it arrives under the FMAs), and the products nobody waits for (v_k = Sig_k s'_k) are not
+// interleaved with the elimination but run afterwards as eight independent, double-buffered passes.
+#ifdef QRW_V2_TIMING
+// clock read that cannot be issued before x is known (predicated on a comparison of x that is practically always true)
+__device__ __forceinline__ long long qrw_clock_after(double x) {
+  long long t = 0;
+  asm volatile("{ .reg .pred q; setp.ne.f64 q, %1, 0d7E37E43C8800759C; @q mov.u64 %0, %%clock64; }" : "+l"(t) : "d"(x) : "memory");
+  return t;
+}
+__shared__ long long chain_stamp[8];  // probe build: clock at the five seams of the chain (lane 0)
+#endif
 QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, int lane) {
+#ifdef QRW_V2_TIMING
+#define QRW_STAMP(n, x) { const long long t_ = qrw_clock_after(x); if (lane == 0) chain_stamp[n] = t_; }
+#else
+#define QRW_STAMP(n, x) ((void)0)
+#endif
+  double lastv = (double)lane;  // what the probe build hangs its clock reads on
+  QRW_STAMP(0, lastv);
   const int i0 = lane & 15;
-  const bool up = lane >= 16;
+  int upi = lane >> 4;  // 0: lower half of the warp (stages 0..7), 1: upper half (stages 15..8)
+  cta::opaque(upi);     // keeps ptxas from cloning the whole chain per half (it did: 468 DFMA instead of 288, run one after the other)
+  const bool up = upi != 0;
   const int i = i0 < 12 ? i0 : 11;
   const bool wr = i0 < 12;
   // stage of this half at elimination step t: lower t, upper 15 - t
-  const int k0 = up ? NS - 1 : 0;
-  const int dk = up ? -1 : 1;
-  double p;
+  const int k0 = (NS - 1) * upi;
+  const int dk = 1 - 2 * upi;
+  double tc[2][12], sn;  // two column buffers: the prefetch must not wait for the registers of the column in use
   {
     double* r0 = rec + SR * k0;
-    p = r0[R_A + i] + r0[R_CC + i];
+    double* r1 = rec + SR * (k0 + dk);
+    const double p = r0[R_A + i] + r0[R_CC + i];
     if (wr) r0[R_SP + i] = p;
+    cta::lds12c<LD>(Tm + MS * (k0 - upi) + i, tc[0]);  // column i of T_0 / U_15
+    sn = r1[R_A + i] + r1[R_CC + i];
   }
 #pragma unroll
   for (int t = 0; t < 7; ++t) {
-    const int kc = k0 + dk * t;       // stage whose s' is broadcast
-    const int kn = kc + dk;           // stage produced
-    const int slot = up ? kc - 1 : kc;
-    const double* Tc = Tm + MS * slot + i;  // column i of T_k / U_k
-    double* rc = rec + SR * kc;
-    double* rn = rec + SR * kn;
-    double tc[12], sg[12];
-#pragma unroll
-    for (int jj = 0; jj < 12; ++jj) tc[jj] = Tc[LD * jj];
-    cta::lds12(Sig + MS * kc + LD * i, sg);
-    const double sn = rn[R_A + i] + rn[R_CC + i];
+    const int kc = k0 + dk * t;  // stage whose s' is broadcast
+    const int kn = kc + dk;      // stage produced
+    double pv[12], sn2 = 0.0;
+    double* tn = tc[(t + 1) & 1];
     cta::wsync();
-    double pv[12];
-    cta::lds12(rc + R_SP, pv);
-    cta::sched_fence();
-    p = sn - dot12(tc, pv);
-    if (wr) rn[R_SP + i] = p;
-    const double v = dot12(sg, pv);
-    if (wr) rc[R_A + i] = v;  // A_k was consumed one step ago
-  }
-  // ---- middle: every lane works on stages 7 / 8
-  cta::wsync();
-  double X;
-  {
-    double* r7 = rec + SR * 7;
-    double* r8 = rec + SR * 8;
-    double tc[12], sg[12], pv[12];
-    const double* Tc = Tm + MS * 7 + i;
-#pragma unroll
-    for (int jj = 0; jj < 12; ++jj) tc[jj] = Tc[LD * jj];
-    cta::lds12(Sig + MS * 7 + LD * i, sg);
-    cta::lds12(r7 + R_SP, pv);
-    cta::sched_fence();
-    const double s8 = r8[R_SP + i] - dot12(tc, pv);
-    const double v7 = dot12(sg, pv);
-    cta::wsync();  // everybody has read s'_8 before it is replaced by s''_8
-    if (wr && !up) {
-      r8[R_SP + i] = s8;
-      r7[R_A + i] = v7;
+    if (t == 3) cta::nb_arrive(1, 64);  // s'_0..3 | s'_15..12 are in shared memory: the helper warp starts on their v_k
+    if (t == 6) cta::nb_arrive(2, 64);  // s'_4..6 | s'_11..9
+    cta::lds12(rec + SR * kc + R_SP, pv);
+    if (t < 6) {  // column i of T_k / U_k of the next step and its right-hand side
+      const double* r2 = rec + SR * (kn + dk);
+      cta::lds12c<LD>(Tm + MS * (kn - upi) + i, tn);
+      sn2 = r2[R_A + i] + r2[R_CC + i];
+    } else {
+      cta::lds12c<LD>(Tm + MS * 7 + i, tn);  // the middle step: column i of T_7 on every lane
     }
-    cta::wsync();
-    cta::lds12(Sig + MS * 8 + LD * i, sg);
-    cta::lds12(r8 + R_SP, pv);
     cta::sched_fence();
-    X = dot12(sg, pv);
-    if (wr && !up) r8[R_XT + i] = X;
+    const double p = sn - dot12(tc[t & 1], pv);
+    if (wr) rec[SR * kn + R_SP + i] = p;
+    lastv = p;
+    sn = sn2;
   }
+  QRW_STAMP(1, lastv);
+  // ---- middle: s''_8 = s'_8 - T_7' s'_7 on every lane, stored by the lower half
+  {
+    double* r8 = rec + SR * 8;
+    double pv[12];
+    cta::wsync();
+    cta::lds12(rec + SR * 7 + R_SP, pv);
+    const double s8p = r8[R_SP + i];
+    cta::sched_fence();
+    const double s8 = s8p - dot12(tc[1], pv);
+    cta::wsync();  // everybody has read s'_8 before it is replaced by s''_8
+    if (wr && !up) r8[R_SP + i] = s8;
+    lastv = s8;
+    cta::wsync();
+  }
+  QRW_STAMP(2, lastv);
+  // ---- v_7 = Sig_7 s'_7 (lower half) and X_8 = Sig_8 s''_8 (upper half); the other v_k come from the helper warp
+  {
+    double sg[12], pv[12];
+    const int kc = 7 + upi;
+    cta::lds12(Sig + MS * kc + LD * i, sg);
+    cta::lds12(rec + SR * kc + R_SP, pv);
+    const double v = dot12(sg, pv);
+    if (wr) rec[SR * kc + R_A + (R_XT - R_A) * upi + i] = v;
+    lastv = v;
+  }
+  QRW_STAMP(3, lastv);
   // ---- back-substitution: lower half stages 7..0, upper half stages 9..15 (idle in the last step)
+  double tr[2][12], vk;
+  cta::lds12(Tm + MS * (7 + upi) + LD * i, tr[0]);  // row i of T_7 / U_9
+  cta::nb_sync(3, 64);  // the helper's v_k are in shared memory
+  vk = rec[SR * (7 + 2 * upi) + R_A + i];
 #pragma unroll
   for (int u = 0; u < 8; ++u) {
-    const int kk = up ? (u < 7 ? 9 + u : 15) : 7 - u;  // stage produced
-    const int kp = up ? kk - 1 : kk + 1;               // stage whose X is broadcast
-    const int slot = up ? kk - 1 : kk;
-    const double* Tr = Tm + MS * slot + LD * i;        // row i of T_k / U_k
-    double* rk = rec + SR * kk;
-    double tr[12], xv[12];
-    cta::lds12(Tr, tr);
-    const double vk = rk[R_A + i];
+    const int kk = u < 7 ? 7 + 2 * upi - dk * u : k0;  // stage produced: 7 - u | 9 + u, the upper half repeats 15
+    const int kp = kk + dk;                            // stage whose X is broadcast
+    double xv[12], vn = 0.0;
+    double* tn = tr[(u + 1) & 1];
     cta::wsync();
     cta::lds12(rec + SR * kp + R_XT, xv);
+    if (u < 7) {
+      const int k2 = u < 6 ? 7 + 2 * upi - dk * (u + 1) : k0;
+      cta::lds12(Tm + MS * (k2 - upi) + LD * i, tn);  // row i of T_k / U_k of the next step
+      vn = rec[SR * k2 + R_A + i];
+    }
     cta::sched_fence();
-    X = vk - dot12(tr, xv);
-    if (wr && (!up || u < 7)) rk[R_XT + i] = X;
+    const double X = vk - dot12(tr[u & 1], xv);
+    if (wr && (!up || u < 7)) rec[SR * kk + R_XT + i] = X;
+    lastv = X;
+    vk = vn;
   }
+  QRW_STAMP(4, lastv);
+}
+
+// The helper warp (the warp next to the chain warp, idle otherwise): v_k = Sig_k s'_k for k = 0..6 (lower half) and 15..9
+// (upper half), parked in the A slot of the stage, in two groups behind the elimination (named barriers 1 and 2); barrier
+// 3 hands them to the back-substitution.  Seven independent products, double-buffered.
+QRW_HDN void state_helper(const double* Sig, double* rec, int lane) {
+  const int i0 = lane & 15;
+  int upi = lane >> 4;
+  cta::opaque(upi);
+  const int i = i0 < 12 ? i0 : 11;
+  const bool wr = i0 < 12;
+  const int k0 = (NS - 1) * upi;
+  const int dk = 1 - 2 * upi;
+  double sg[2][12], pv[2][12];
+  cta::lds12(Sig + MS * k0 + LD * i, sg[0]);
+  cta::nb_sync(1, 64);
+  cta::lds12(rec + SR * k0 + R_SP, pv[0]);
+#pragma unroll
+  for (int t = 0; t < 7; ++t) {
+    const int kc = k0 + dk * t;
+    if (t < 6) {
+      const int k2 = kc + dk;
+      cta::lds12(Sig + MS * k2 + LD * i, sg[(t + 1) & 1]);
+      if (t == 3) cta::nb_sync(2, 64);
+      cta::lds12(rec + SR * k2 + R_SP, pv[(t + 1) & 1]);
+    }
+    const double v = dot12(sg[t & 1], pv[t & 1]);
+    if (wr) rec[SR * kc + R_A + i] = v;
+  }
+  cta::wsync();
+  cta::nb_arrive(3, 64);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -733,6 +799,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
   // (5: everything before the loop, 6: factorisations, 7: residual checks).  Parked in the last entries of the debug dump.
   long long tq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tp[7] = {0, 0, 0, 0, 0, 0, 0};  // phases (1)..(7) one by one
+  long long tcs[4] = {0, 0, 0, 0};          // inside the chain: elimination, middle, v products, back-substitution
   const int tw = ((recw + 1) & 7) * 32;
   tq[5] = qrw_clock() - t_entry;
 #define QRW_TICK(i, t0) tq[i] += qrw_clock() - (t0)
@@ -832,8 +899,14 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
     // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
     if (w == recw) state_recurrence(S.Sig, S.T, S.rec, l);
+    else if (w == ((recw + 1) & 7)) state_helper(S.Sig, S.rec, l);
 #ifdef QRW_V2_TIMING
-    if (w == recw) QRW_TICK(4, tA);
+    if (w == recw) {
+      QRW_TICK(4, tA);
+      cta::wsync();
+      const volatile long long* cs = chain_stamp;
+      for (int q = 0; q < 4; ++q) tcs[q] += cs[q + 1] - cs[q];
+    }
 #endif
     cta::bar();
 #ifdef QRW_V2_TIMING
@@ -1039,7 +1112,10 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
       for (int i = 5; i < 8; ++i) dbg[1273 + i] = (double)tq[i];
       for (int i = 0; i < 7; ++i) dbg[1260 + i] = (double)tp[i];
     }
-    if (w == recw && l == 0) dbg[1276] = (double)tq[4];
+    if (w == recw && l == 0) {
+      dbg[1276] = (double)tq[4];
+      for (int q = 0; q < 4; ++q) dbg[1267 + q] = (double)tcs[q];
+    }
     if (tid == 0) dbg[1277] = (double)(iter > C.max_iter ? C.max_iter : iter);
   }
 #endif

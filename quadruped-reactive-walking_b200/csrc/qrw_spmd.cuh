@@ -92,6 +92,13 @@ __device__ __forceinline__ void lds12(const double* p, double* v) {
   for (int i = 0; i < 12; i += 2)
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
 }
+// v[i] = p[STRIDE * i], i = 0..11 (a column of a padded 12x12 block) as twelve LDS.64 that stay where they are written
+template <int STRIDE>
+__device__ __forceinline__ void lds12c(const double* p, double* v) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+#pragma unroll
+  for (int i = 0; i < 12; ++i) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[i]) : "r"(a + 8 * STRIDE * i));
+}
 // v[0..5] = p[0..5] (16-byte aligned) as three LDS.128 issued back to back
 __device__ __forceinline__ void lds6(const double* p, double* v) {
   const unsigned a = (unsigned)__cvta_generic_to_shared(p);
@@ -99,6 +106,11 @@ __device__ __forceinline__ void lds6(const double* p, double* v) {
   for (int i = 0; i < 6; i += 2)
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
 }
+// named barriers of the CTA (ids 1..15; 0 is __syncthreads): `nthreads` = arriving + waiting threads, a multiple of 32
+__device__ __forceinline__ void nb_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+__device__ __forceinline__ void nb_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+// the value becomes unknown to the compiler (no instruction is emitted)
+__device__ __forceinline__ void opaque(int& v) { asm volatile("" : "+r"(v)); }
 // Scheduling fence for ptxas: a warp barrier is never crossed by its instruction scheduler, so the loads issued
 // before it stay grouped ahead of the arithmetic that follows (costs one issue slot).
 __device__ __forceinline__ void sched_fence() { __syncwarp(); }
@@ -117,11 +129,18 @@ int fetch_add(int* p, int v);
 double shfl16(double v, int src);
 double shfl_xor(double v, int m);
 inline void sched_fence() {}
+inline void opaque(int&) {}
+void nb_arrive(int id, int nthreads);
+void nb_sync(int id, int nthreads);
 inline void lds12(const double* p, double* v) {
   for (int i = 0; i < 12; ++i) v[i] = p[i];
 }
 inline void lds6(const double* p, double* v) {
   for (int i = 0; i < 6; ++i) v[i] = p[i];
+}
+template <int STRIDE>
+inline void lds12c(const double* p, double* v) {
+  for (int i = 0; i < 12; ++i) v[i] = p[STRIDE * i];
 }
 }  // namespace cta
 }  // namespace qrw

@@ -42,7 +42,9 @@ qrw_emu_switch:
 )");
 
 struct Emu {
-  enum { RUN = 0, AT_BAR = 1, AT_WSYNC = 2, DONE = 3 };
+  enum { RUN = 0, AT_BAR = 1, AT_WSYNC = 2, DONE = 3, AT_NAMED = 4 };
+  int nb_count[16] = {0};   // named barriers (bar.arrive / bar.sync id, count): threads seen so far
+  std::vector<int> nb_id;   // id a thread in AT_NAMED waits on
   int n = 0, cur = -1;
   std::vector<void*> sp;
   std::vector<char*> stacks;
@@ -76,6 +78,7 @@ inline void run_cta(int nthreads, std::function<void()> body) {
   e.stacks.resize(nthreads);
   e.state.assign(nthreads, Emu::RUN);
   e.xch.assign(nthreads, 0.0);
+  e.nb_id.assign(nthreads, -1);
   for (int t = 0; t < nthreads; ++t) {
     char* st = (char*)aligned_alloc(64, Emu::STACK);
     e.stacks[t] = st;
@@ -134,6 +137,21 @@ inline void run_cta(int nthreads, std::function<void()> body) {
 inline int tid() { return g_emu->cur; }
 inline void bar() { yield_as(Emu::AT_BAR); }
 inline void wsync() { yield_as(Emu::AT_WSYNC); }
+// named barrier `id` completes when `nthreads` threads have arrived (bar.arrive: without waiting, bar.sync: waiting)
+inline bool nb_count_in(int id, int nthreads) {
+  Emu* e = g_emu;
+  if (++e->nb_count[id] < nthreads) return false;
+  e->nb_count[id] = 0;
+  for (int t = 0; t < e->n; ++t)
+    if (e->state[t] == Emu::AT_NAMED && e->nb_id[t] == id) e->state[t] = Emu::RUN;
+  return true;
+}
+inline void nb_arrive(int id, int nthreads) { nb_count_in(id, nthreads); }
+inline void nb_sync(int id, int nthreads) {
+  if (nb_count_in(id, nthreads)) return;
+  g_emu->nb_id[g_emu->cur] = id;
+  yield_as(Emu::AT_NAMED);
+}
 inline double shfl(double v, int src) {
   Emu* e = g_emu;
   const int t = e->cur;

@@ -21,6 +21,8 @@ for B in (148, 296, 4096):
     d = m.debug()["bounds"]  # last 192 entries of the dump; the probe build parks its counters at [183:189]
     ph = d[:, 171:178] / d[:, 188][:, None]
     print(f"B={B:5d}: cycles per iteration by phase (1)..(7): " + " ".join(f"{x:6.0f}" for x in ph.mean(0)))
+    cs = d[:, 178:182] / d[:, 188][:, None]
+    print(f"B={B:5d}: cycles per iteration inside the chain: elimination {cs[:,0].mean():6.0f} | middle {cs[:,1].mean():6.0f} | v products {cs[:,2].mean():6.0f} | back-substitution {cs[:,3].mean():6.0f}")
     t = d[:, 183:192]
     it = t[:, 5]
     per = t[:, :5] / it[:, None]
