@@ -27,3 +27,6 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:plan
 echo "ncu planner rc=$?" | tee -a $OUT/rc.txt
 for r in prof_mpc prof_wbc prof_planner; do ncu -i $OUT/$r.ncu-rep --page raw --csv > $OUT/${r}_raw.csv 2>/dev/null; done
 ls -la $OUT
+timeout 60 tools/chain_bench.bin > $OUT/chain_bench.txt 2>&1; timeout 60 tools/chain_bench_t.bin >> $OUT/chain_bench.txt 2>&1
+[ -f tools/libqrw_timing.so ] && QRW_LIB=$PWD/tools/libqrw_timing.so timeout 200 python tools/timing_probe.py > $OUT/timing_probe.txt 2>&1
+echo "probes rc=$?" | tee -a $OUT/rc.txt
