@@ -772,8 +772,8 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     c_temp = limit_scaling(c_temp);
     cscale *= 1.0 / c_temp;
   }
+  if (tid == 0) S.red[120] = cscale;  // parked for factor() and the residual checks; published by the barrier below
   cta::bar();
-  if (tid == 0) S.red[120] = cscale;
   if (dbg && isv) {
     dbg[gvar(k, j)] = R.dF;
     dbg[gvar(k, 12 + j)] = R.dX;

@@ -55,6 +55,10 @@ struct Emu {
   static constexpr size_t STACK = 256 * 1024;
 };
 inline thread_local Emu* g_emu = nullptr;
+// order in which the scheduler sweeps the runnable fibers: 0 ascending thread id, 1 descending, 2 odd warps first (lanes descending),
+// 3 warps descending, 4 lanes descending.
+// Every order is a legal CUDA schedule; code without races between collectives gives bit-identical results in all of them.
+inline int g_sweep_order = 0;
 
 inline void fiber_entry() {
   Emu* e = g_emu;
@@ -94,7 +98,16 @@ inline void run_cta(int nthreads, std::function<void()> body) {
   for (;;) {
     bool progress = false;
     int alive = 0;
-    for (int t = 0; t < nthreads; ++t) {
+    for (int tt = 0; tt < nthreads; ++tt) {
+      int t = tt;
+      if (g_sweep_order == 1) t = nthreads - 1 - tt;
+      else if (g_sweep_order == 3) t = (nthreads / 32 - 1 - tt / 32) * 32 + (tt & 31);  // warps descending, lanes ascending
+      else if (g_sweep_order == 4) t = (tt & ~31) + 31 - (tt & 31);                       // warps ascending, lanes descending
+      else if (g_sweep_order == 2 && nthreads > 32) {
+        const int nw = nthreads / 32, w = tt / 32;
+        const int wsel = w < nw / 2 ? 2 * w + 1 : 2 * (w - nw / 2);  // 1, 3, 5, .., 0, 2, 4, ..
+        t = (wsel < nw ? wsel : w) * 32 + 31 - (tt & 31);
+      }
       if (e.state[t] == Emu::RUN) {
         e.cur = t;
         qrw_emu_switch(&e.sched_sp, e.sp[t]);

@@ -15,6 +15,8 @@ using namespace qrw;
 extern "C" {
 
 int emu_mpc_state_doubles() { return MPC_STATE_DOUBLES; }
+// 0 / 1 / 2: order in which the emulated threads of a CTA are run between collectives (cta_emu.hpp)
+void emu_set_schedule(int order) { qrw::cta::g_sweep_order = order; }
 int emu_mpc_state_ints() { return MPC_STATE_INTS; }
 
 // Same contract as the CUDA kernel: instance-major inputs, persistent state, outputs.
@@ -117,6 +119,7 @@ extern "C" void emu_mpc_v2_run(int B, double dt, int N_gait, int first, int max_
                          out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8);
       });
     }
+    if (nthreads <= 1) g_last_slab = slab;
   };
   if (nthreads <= 1) {
     nthreads = 1;

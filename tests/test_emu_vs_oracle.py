@@ -73,6 +73,34 @@ def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
         x0 = ro[:, :12].copy()
 
 
+@pytest.mark.parametrize("core", ["v2", "cta"])
+def test_mpc_result_does_not_depend_on_the_thread_schedule(emu, core):
+    """Race check without a GPU: between two collectives the emulator may run the threads of a CTA in any order (every order
+    is a legal CUDA schedule).  The chain / helper warps of the v2 core hand data over through named barriers; a missing
+    barrier shows up as a result that depends on the order."""
+    from qrw_b200 import workloads as wl
+
+    B, ticks = 6, 3
+    w = wl.MpcWorkload(B, 5, gaits=GAITS, ticks=ticks + 1)
+    runs = []
+    try:
+        for order in (0, 1, 2, 3, 4):
+            emu.emu_set_schedule(order)
+            e, x0, outs = EmuMPC(emu, B, core=core), None, []
+            for t in range(ticks):
+                xr, fs = w.inputs(t, x0)
+                e.run(t, xr, fs)
+                outs.append((e.out.copy(), e.info.copy(), e.std.copy()))
+                x0 = e.out.reshape(B, 16, 24)[:, 0, :12].copy()
+            runs.append(outs)
+    finally:
+        emu.emu_set_schedule(0)
+    for other in runs[1:]:
+        for (o0, i0, s0), (o1, i1, s1) in zip(runs[0], other):
+            assert np.array_equal(i0, i1)
+            assert np.array_equal(o0, o1) and np.array_equal(s0, s1)  # bit for bit
+
+
 @pytest.mark.parametrize("core", ["v2", "cta", "warp"])
 def test_mpc_scaling_and_bounds(emu, oracle, core):
     from qrw_b200 import workloads as wl
