@@ -17,6 +17,7 @@ struct EmuPlanner {
   std::vector<unsigned long long> bits;
   std::vector<int> flags;
 };
+int g_lane_order = 0;
 }  // namespace
 
 extern "C" {
@@ -62,12 +63,19 @@ void emu_planner_run(void* h, int k, int stages, const double* q7, const double*
   const int N = P->C.N_gait;
   for (int b = 0; b < P->M.B; ++b) {
     LaneCtx X[4];
-    for (int j = 0; j < 4; ++j)
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = g_lane_order ? 3 - jj : jj;
       lane_compute(P->C, P->M, b, j, k, stages, q7 + 7 * b, v6 + 6 * b, vref6 + 6 * b, code ? code[b] : 0,
                    P->fsteps.data() + (size_t)b * N * 12 + 3 * N * j, X[j]);
-    for (int j = 0; j < 4; ++j) lane_store(P->C, P->M, b, j, X[j]);
+    }
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = g_lane_order == 1 ? 3 - jj : jj;
+      lane_store(P->C, P->M, b, j, X[j]);
+    }
   }
 }
+// 0: lanes 0..3 in both phases, 1: 3..0 in both, 2: compute 3..0, store 0..3 (every order is a legal GPU schedule)
+void emu_planner_set_lane_order(int order) { g_lane_order = order; }
 
 // which: 0 xref, 1 fsteps, 2..: a [B][len] field of the state (field offset = which - 2)
 void emu_planner_get(void* h, int which, int len, double* out) {

@@ -260,6 +260,24 @@ def test_emulated_stages_one_by_one_equal_the_fused_tick(emu):
             assert (A.get(n) == S.get(n)).all(), (k, n)
 
 
+def test_emulated_planner_does_not_depend_on_the_lane_order(emu):
+    """The four lanes of a robot exchange data only through the __syncwarp between lane_compute and lane_store: any order
+    of the lanes inside a phase must give the same bits (race check without a GPU)."""
+    B = 12
+    W = wl.PlannerWorkload(B, 7, codes=(1, 2, 3, 4), change_every=40)
+    P = [EmuPlanner(emu, B) for _ in range(3)]
+    try:
+        for k in range(170):
+            q7, hv, vr, code = W.tick(k)
+            for order, p in enumerate(P):
+                emu.emu_planner_set_lane_order(order)
+                p.run(k, q7, hv, vr, code)
+            for n in ("xref", "fsteps", "gait", "past", "desired") + FIELDS:
+                assert (P[0].get(n) == P[1].get(n)).all() and (P[0].get(n) == P[2].get(n)).all(), (k, n)
+    finally:
+        emu.emu_planner_set_lane_order(0)
+
+
 # ------------------------------------------------------------------------------------------ CUDA vs oracle (GPU)
 @pytest.mark.gpu
 @pytest.mark.parametrize("B,seed,codes", [(37, 1, (1, 2, 3, 4)), (256, 2, (3, 5))])
