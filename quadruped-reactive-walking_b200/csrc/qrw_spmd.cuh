@@ -23,7 +23,12 @@
 #else
 #define QRW_HD inline
 #define QRW_HDN inline
-#define QRW_LANES(l) for (int l = 0; l < 32; ++l)
+// lanes of a phase one after the other, ascending or (qrw::g_emu_lanes_descending, set by the tests) descending: a phase that
+// keeps the rules below gives the same bits either way
+namespace qrw {
+inline int g_emu_lanes_descending = 0;
+}
+#define QRW_LANES(l) for (int _i = 0, l = qrw::g_emu_lanes_descending ? 31 : 0; _i < 32; ++_i, l += qrw::g_emu_lanes_descending ? -1 : 1)
 #define QRW_SYNC() ((void)0)
 #define QRW_ON_GPU 0
 #include <cmath>

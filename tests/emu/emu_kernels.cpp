@@ -17,6 +17,8 @@ extern "C" {
 int emu_mpc_state_doubles() { return MPC_STATE_DOUBLES; }
 // 0 / 1 / 2: order in which the emulated threads of a CTA are run between collectives (cta_emu.hpp)
 void emu_set_schedule(int order) { qrw::cta::g_sweep_order = order; }
+// warp-SPMD cores (mpc_core.cuh, wbc_core.cuh): lanes of a phase ascending (0) or descending (1)
+void emu_set_lanes_descending(int on) { qrw::g_emu_lanes_descending = on; }
 int emu_mpc_state_ints() { return MPC_STATE_INTS; }
 
 // Same contract as the CUDA kernel: instance-major inputs, persistent state, outputs.

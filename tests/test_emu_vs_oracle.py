@@ -174,6 +174,38 @@ def test_wbc_three_calls(emu, oracle):
         np.testing.assert_allclose(H, Hc, rtol=1e-12, atol=1e-12)
 
 
+def test_warp_cores_do_not_depend_on_the_lane_order(emu):
+    """wbc_core.cuh / mpc_core.cuh run the 32 lanes of a phase one after the other in emulation; a phase that reads what
+    another lane writes in the same phase (a missing __syncwarp on the GPU) gives different bits with the lanes reversed."""
+    from qrw_b200 import workloads as wl
+
+    B = 16
+    res = []
+    try:
+        for desc in (0, 1):
+            emu.emu_set_lanes_descending(desc)
+            st = np.zeros((B, emu.emu_wbc_state_doubles()))
+            f_res, ddq, H, info = np.zeros((B, 12)), np.zeros((B, 6)), np.zeros((B, 144)), np.zeros((B, 4), np.int32)
+            got = []
+            for call in range(3):
+                M, Jc, f, R = wl.wbc_inputs(B, seed=30 + call)
+                emu.emu_wbc_run(B, int(call == 0), _p(M), _p(Jc), _p(f), _p(R), _p(st), _p(f_res), _p(ddq), _p(H), _p(info))
+                got.append((f_res.copy(), ddq.copy(), H.copy(), info.copy(), st.copy()))
+            w = wl.MpcWorkload(4, 3, gaits=GAITS, ticks=3)
+            e, x0 = EmuMPC(emu, 4, core="warp"), None
+            for t in range(2):
+                xr, fs = w.inputs(t, x0)
+                e.run(t, xr, fs)
+                got.append((e.out.copy(), e.info.copy(), e.std.copy()))
+                x0 = e.out.reshape(4, 16, 24)[:, 0, :12].copy()
+            res.append(got)
+    finally:
+        emu.emu_set_lanes_descending(0)
+    for a, b in zip(res[0], res[1]):
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+
+
 def test_invkin(emu, oracle):
     from qrw_b200 import workloads as wl
 
