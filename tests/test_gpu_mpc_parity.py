@@ -132,6 +132,38 @@ def test_state_snapshot_replays_identically():
     assert np.array_equal(a, gpu.get_latest_result())
 
 
+def test_results_do_not_depend_on_which_cta_solves_which_robot():
+    """Race check on the GPU: a persistent CTA solves ~14 robots one after the other in the same shared-memory slab, and which
+    robot follows which depends on the work order.  Anything read before it is (re)written -- a missing barrier, a stale value
+    left by the previous robot -- makes the result depend on that order.  Two handles with different work orders, mixed gaits
+    (consecutive robots differ), three ticks: results, iteration counts and the persistent solver state must be bit-identical."""
+    import torch
+
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 4096
+    w = wl.MpcWorkload(B, 17, gaits=("trot", "walk", "bounding", "pacing", "static"), ticks=4)
+    a, b = BatchedMPC(B), BatchedMPC(B)
+    b.set_work_order(True)
+    x0 = None
+    for t in range(3):
+        xr, fs = w.inputs(t, x0)
+        a.run(t, xr, fs)
+        b.run(t, xr, fs)
+        ra, rb = a.get_latest_result(), b.get_latest_result()
+        assert np.array_equal(a.info()["iters"], b.info()["iters"]), f"tick {t}"
+        assert np.array_equal(ra, rb), f"tick {t}: {np.abs(ra - rb).max()}"
+        sa = torch.empty(a.state_bytes(), dtype=torch.uint8, device="cuda")
+        sb = torch.empty(b.state_bytes(), dtype=torch.uint8, device="cuda")
+        a.state_save(sa)
+        b.state_save(sb)
+        torch.cuda.synchronize()
+        assert torch.equal(sa, sb), f"solver state differs at tick {t}"
+        x0 = ra[:, :12].copy()
+    a.close()
+    b.close()
+
+
 def test_device_pointer_path_matches_host_path():
     import torch
 
