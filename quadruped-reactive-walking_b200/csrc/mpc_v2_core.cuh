@@ -354,6 +354,18 @@ QRW_HD double dot12(const double* m, const double* v) {
   }
   return (a0 + a1) + (a2 + a3);
 }
+// c - m.v with c folded into the first partial sum: one addition less on the dependent path of a chain step
+QRW_HD double sub_dot12(double c, const double* m, const double* v) {
+  double a0 = -c, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+  for (int jj = 8; jj >= 0; jj -= 4) {
+    a0 += m[jj] * v[jj];
+    a1 += m[jj + 1] * v[jj + 1];
+    a2 += m[jj + 2] * v[jj + 2];
+    a3 += m[jj + 3] * v[jj + 3];
+  }
+  return -(a0 + a1) - (a2 + a3);
+}
 // same product with the four partial sums accumulated in ascending order (the order phase (3) has always used)
 QRW_HD double dot12a(const double* m, const double* v) {
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
@@ -424,7 +436,7 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
       cta::lds12c<LD>(Tm + MS * 7 + i, tn);  // the middle step: column i of T_7 on every lane
     }
     cta::sched_fence();
-    const double p = sn - dot12(tc[t & 1], pv);
+    const double p = sub_dot12(sn, tc[t & 1], pv);
     if (wr) rec[SR * kn + R_SP + i] = p;
     lastv = p;
     sn = sn2;
@@ -438,7 +450,7 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
     cta::lds12(rec + SR * 7 + R_SP, pv);
     const double s8p = r8[R_SP + i];
     cta::sched_fence();
-    const double s8 = s8p - dot12(tc[1], pv);
+    const double s8 = sub_dot12(s8p, tc[1], pv);
     cta::wsync();  // everybody has read s'_8 before it is replaced by s''_8
     if (wr && !up) r8[R_SP + i] = s8;
     lastv = s8;
@@ -475,7 +487,7 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
       vn = rec[SR * k2 + R_A + i];
     }
     cta::sched_fence();
-    const double X = vk - dot12(tr[u & 1], xv);
+    const double X = sub_dot12(vk, tr[u & 1], xv);
     if (wr && (!up || u < 7)) rec[SR * kk + R_XT + i] = X;
     lastv = X;
     vk = vn;
