@@ -471,8 +471,7 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
   // ---- back-substitution: lower half stages 7..0, upper half stages 9..15 (idle in the last step)
   double tr[2][12], vk;
   cta::lds12(Tm + MS * (7 + upi) + LD * i, tr[0]);  // row i of T_7 / U_9
-  cta::nb_sync(3, 64);  // the helper's v_k are in shared memory
-  vk = rec[SR * (7 + 2 * upi) + R_A + i];
+  vk = 0.0;
 #pragma unroll
   for (int u = 0; u < 8; ++u) {
     const int kk = u < 7 ? 7 + 2 * upi - dk * u : k0;  // stage produced: 7 - u | 9 + u, the upper half repeats 15
@@ -484,10 +483,20 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
     if (u < 7) {
       const int k2 = u < 6 ? 7 + 2 * upi - dk * (u + 1) : k0;
       cta::lds12(Tm + MS * (k2 - upi) + LD * i, tn);  // row i of T_k / U_k of the next step
-      vn = rec[SR * k2 + R_A + i];
+      if (u > 0) vn = rec[SR * k2 + R_A + i];
     }
     cta::sched_fence();
-    const double X = sub_dot12(vk, tr[u & 1], xv);
+    double X;
+    if (u == 0) {
+      // the first step waits for the helper's v_k behind its product, not in front of it
+      const double d = dot12(tr[0], xv);
+      cta::nb_sync(3, 64);
+      vk = rec[SR * kk + R_A + i];
+      vn = rec[SR * (7 + 2 * upi - dk) + R_A + i];
+      X = vk - d;
+    } else {
+      X = sub_dot12(vk, tr[u & 1], xv);
+    }
     if (wr && (!up || u < 7)) rec[SR * kk + R_XT + i] = X;
     lastv = X;
     vk = vn;
