@@ -44,8 +44,8 @@ METRIC = "Solo12 MPC QP solves/sec (batched, 16-step)"
 UNIT = "solves/s"
 BYTES_PER_SOLVE = 35340  # in 3,556 + out 3,080 + warm-start state r/w 28,704
 # dram__bytes_read.sum + dram__bytes_write.sum of one mpc_v2_kernel launch over 4096 robots, ncu --set full
-# (profiles/r01c_ncu_mpc_v2.txt: 89.51 MB + 50.11 MB), per robot: no re-reads beyond the algorithmic bytes
-NCU_DRAM_BYTES_PER_SOLVE = (89.505024e6 + 50.108672e6) / 4096
+# (profiles/r01f_ncu_mpc_v2.txt: 89.76 MB + 49.09 MB), per robot: no re-reads beyond the algorithmic bytes
+NCU_DRAM_BYTES_PER_SOLVE = (89.755392e6 + 49.092096e6) / 4096
 WORKLOAD = "4096 batched Solo12 trot MPC instances per GPU, randomised states/velocity refs, update ticks (warm start)"
 
 
@@ -390,7 +390,7 @@ def run_b200(args):
     achieved = BYTES_PER_SOLVE * B / (kern_ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
             "frac": achieved / peaks["hbm_gbs"], "traffic": NCU_DRAM_BYTES_PER_SOLVE * B, "peak_source": which,
-            "traffic_source": "ncu --set full, profiles/r01c_ncu_mpc_v2.txt, scaled by batch",
+            "traffic_source": "ncu --set full, profiles/r01f_ncu_mpc_v2.txt, scaled by batch",
             "kernel": "mpc_v2_kernel", "algorithmic_bytes_per_solve": BYTES_PER_SOLVE}
     fp64 = None
     if hasattr(L, "qrw_fp64_peak"):
