@@ -21,7 +21,16 @@
 //     iterates live in registers of their owner; everything else a stage owns (exchange buffers, D, E, B_k,
 //     F^-1, GF, M) sits in one shared-memory record.  Stage-internal exchanges use __syncwarp; only the
 //     state chain (a noinline call, one warp) needs the two CTA barriers of an iteration.
-//   * 108 KB of shared memory and 128 registers: two CTAs (16 warps) per SM.
+//   * 89 KB of shared memory and 128 registers: two CTAs (16 warps) per SM.
+//   * (round 2) the matrix rows a lane reads again in every iteration live in TENSOR MEMORY, not in shared memory:
+//     F_k^-1 (row j of its owner thread) and the rows / columns of T_k, U_k, Sig_k the three chain warps walk through.
+//     ncu on round 1 (profiles/r01f_ncu_mpc_v2.txt) had the SM's shared-memory pipe at 0.51 wavefronts per cycle and the
+//     chain -- a sequence of dependent shared-memory round trips -- 1.8x slower inside the kernel than alone, because the
+//     co-resident CTA's LDS bursts queue in front of it.  tcgen05.ld (32x32b: a thread reads columns of its own TMEM
+//     lane) goes through a separate pipe: measured 840 B/cycle/SM, no interference with LDS in either direction
+//     (tools/tmem_bench.cu, profiles/r02_tmem_bench.txt).  256 columns per CTA (two CTAs share the SM's 512): columns
+//     [0, 48) hold the F^-1 rows of the two warps of a lane quadrant, [48, 240) the eight rows of the chain role that
+//     runs in that quadrant.  No tcgen05.mma anywhere: the tensor cores have no f64 kind, their memory is what is used.
 // It is still an exact solve of the same KKT system: the iterates differ from OSQP's by round-off only.
 #pragma once
 #include "mpc_core.cuh"
@@ -58,8 +67,11 @@ constexpr int R_BANG = 180;  // [3][12] angular block of B_k (unscaled)
 constexpr int R_B1 = 216;  // [12] scaled right-hand side of the dynamics rows
 constexpr int R_GF = 228;  // [6][14] rows 6..11 of GF = E B0 D_f F^-1 (what the dynamics rows see of a force right-hand side)
 constexpr int R_MR = 312;  // [6][6]  M = GF D_f B0' E (rows 6..11 x rows 6..11)
-constexpr int R_FI = 348;  // [12][14] F_k^-1 (in registers it was spilled to local memory around the chain call)
-constexpr int SR = 516;
+constexpr int SR = 348;    // (F_k^-1 left the record for tensor memory in round 2)
+// tensor-memory columns of a lane quadrant (32-bit columns; a row of 12 doubles = 24 columns)
+constexpr int TM_FI = 0;     // [2][24] row j of F_k^-1 of the thread: warps 0..3 at column 0, warps 4..7 at column 24
+constexpr int TM_ROLE = 48;  // [8][24] rows of the chain role of this quadrant's warp (elimination / helper / back-substitution)
+static_assert(TM_ROLE + 8 * 24 <= cta::TMEM_COLS, "tensor-memory columns of a CTA");
 constexpr int V_W = V_REC + 16 * SR;  // [144] Gauss-Jordan ping-pong / T_k staging of the factorisation
 constexpr int V_RED = V_W + 144;      // 128   reductions
 constexpr int V_INT = V_RED + 128;    // 128 ints
@@ -71,6 +83,7 @@ constexpr int R_N = 72;  // [36]    N_k (6x6); dead after step (d)
 static_assert(R_N + 36 <= R_D, "factorisation scratch overruns the record");
 static_assert((SR * 8) % 16 == 0 && (V_REC * 8) % 16 == 0, "records must keep 16-byte alignment");
 static_assert(V2_SLAB_BYTES <= 112 * 1024, "two CTAs per SM need <= 113 KB each");
+constexpr int V2_TMEM_SLOT = 120;  // index in the int buffer where tcgen05.alloc parks the CTA's tensor-memory base address
 
 struct Sm {
   double *Sig, *T, *rec, *W, *red;
@@ -83,7 +96,7 @@ struct Sm {
 QRW_HD int grow(int k, int r) { return r < 12 ? 12 * k + r : (r < 24 ? 192 + 12 * k + (r - 12) : 384 + 20 * k + (r - 24)); }
 
 // per-thread registers of variable lane j = 3 foot + axis of stage k (lanes 12..15 of a stage idle):
-//   row j of F_k^-1 and GF and column j of B_k live in the record (R_FI, R_GF, R_BANG)
+//   row j of F_k^-1 lives in tensor memory (TM_FI), row j of GF and column j of B_k in the record (R_GF, R_BANG)
 //   xf, xX: scaled iterates of f_k[j], X_{k+1}[j]; z1, y1, e1: dynamics row (k,j); y2: force-enable row (k,j)
 //   friction-cone rows of the foot, two slots: axis x -> rows 0,1 (+-fx - mu fz), axis y -> rows 2,3, axis z -> row 4 (-fz)
 //   in slot A and nothing in slot B
@@ -108,12 +121,12 @@ QRW_HD double b0_row(const MpcConst& C, const double* Bk, const double* v, int r
 
 // ------------------------------------------------------------------------------------------
 // Factorisation of K, forces first.  All threads of the CTA; ends with a CTA barrier.
-//   F_k   = K(f_k, f_k)                                   -> record (R_FI: inverse; R_GF, R_MR: GF and M)
+//   F_k   = K(f_k, f_k)                                   -> inverse: tensor memory (TM_FI); GF and M: record (R_GF, R_MR)
 //   N_k   = e^2 (B0 D_f F_k^-1 D_f B0') e^2  (6 x 6)      -> record scratch
 //   G_kk, G_{k,k+1}: Schur complement on the states       -> Sig / T slots, then the twisted block LDL'
 //   (pivot inverses Sig_k, coupling matrices T_k = Sig_k G_{k,k+1} for k <= 7, U_k = Sig_k G_{k-1,k}' for k >= 9)
 // ------------------------------------------------------------------------------------------
-QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, double cscale, int tid) {
+QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, double cscale, int tid, int recw, unsigned tm) {
   const int k = tid >> 4, j = tid & 15;
   const bool isv = j < 12;
   const int c3 = j % 3, ft = isv ? j / 3 : 0;
@@ -188,10 +201,10 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
       for (int c = 0; c < 12; ++c) F[c] = (c == p) ? -f * d : F[c] - f * (pr[c] * d);
     }
   }
+  // row j of F_k^-1 goes to the thread's own tensor-memory lane (warp-uniform: lanes 12..15 park their unit row)
+  cta::tmem_st12(tm + TM_FI + 24 * (tid >> 7), F);
   // ---- (c) Y(j, r) = sum_b Finv(j,b) D_f(b) B0(6+r, b), r = 0..5
   if (isv) {
-#pragma unroll
-    for (int b = 0; b < 12; ++b) rec[R_FI + LD * j + b] = F[b];
     double y[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int b = 0; b < 12; ++b) {
@@ -331,6 +344,30 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
   // the scratch overlapped CC of the last stage, which nobody writes and the recurrence reads as zero
   if (tid < 12) S.rec[SR * (NS - 1) + R_CC + tid] = 0.0;
   cta::bar();
+  // ---- (f) the three chain warps copy the rows they walk through in every iteration into their tensor-memory lanes
+  // (TM_ROLE + 24 t = what step t of the role reads); lanes 12..15 of a half-warp duplicate row 11
+  const int w = tid >> 5, role = (w - recw) & 7;
+  if (role < 3) {
+    const int lane = tid & 31, upi = lane >> 4, i0 = lane & 15, i = i0 < 12 ? i0 : 11;
+    const int k0 = (NS - 1) * upi, dk = 1 - 2 * upi;
+    for (int t = 0; t < 8; ++t) {
+      double c[12];
+      if (role == 0) {
+        // elimination: column i of T_t | U_{15-t} (t < 7), of T_7 for the middle step
+        const int slot = t < 7 ? k0 + dk * t - upi : 7;
+        cta::lds12c<LD>(S.T + MS * slot + i, c);
+      } else if (role == 1) {
+        // helper: row i of Sig_t | Sig_{15-t}, t < 7
+        cta::lds12(S.Sig + MS * (k0 + dk * (t < 7 ? t : 6)) + LD * i, c);
+      } else {
+        // back-substitution: row i of T_7, .., T_0 | U_9, .., U_15 (the upper half repeats its last row)
+        const int k2 = t == 0 ? 7 + 2 * upi : (t < 7 ? 7 + 2 * upi - dk * t : k0);
+        cta::lds12(S.T + MS * (k2 - upi) + LD * i, c);
+      }
+      cta::tmem_st12(tm + TM_ROLE + 24 * t, c);
+    }
+  }
+  cta::tmem_wait_st();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -378,11 +415,14 @@ QRW_HD double dot12a(const double* m, const double* v) {
   }
   return (a0 + a1) + (a2 + a3);
 }
-// Scheduling (v2.7): a step is one dependent sequence  STS -> LDS.128 x6 (the broadcast) -> 3 DFMA deep -> 3 DADD -> STS.
-// Shared memory serves a warp's requests in order, so every load issued between the store and the broadcast loads of
-// the next step delays that step: the matrix column / row of step t+1 is therefore requested in step t, right behind
-// the broadcast loads (it arrives under the FMAs), and the products nobody waits for (v_k = Sig_k s'_k) are not
-// interleaved with the elimination but run afterwards as eight independent, double-buffered passes.
+// Scheduling: a step is one dependent sequence  STS -> LDS.128 x6 (the broadcast) -> 3 DFMA deep -> 3 DADD -> STS.
+// The matrix column / row of step t+1 comes from the lane's tensor memory: it is requested in step t, right behind the
+// wait for the row of step t (tcgen05.wait::ld waits for everything outstanding, so one request is in flight at a time),
+// and arrives under the FMAs without touching the shared-memory queue the broadcast of the next step goes through.
+// Three warps share the work (round 2; each reads its rows from its own lane quadrant of tensor memory):
+//   E (warp recw)     elimination and the middle step; hands s'_k to H (named barriers 1, 2) and X_8 | v_7 to S (barrier 4)
+//   H (warp recw + 1) v_k = Sig_k s'_k for k = 0..6 | 15..9, behind the elimination (barrier 3 hands them to S)
+//   S (warp recw + 2) back-substitution
 #ifdef QRW_V2_TIMING
 // clock read that cannot be issued before x is known (predicated on a comparison of x that is practically always true)
 __device__ __forceinline__ long long qrw_clock_after(double x) {
@@ -390,14 +430,12 @@ __device__ __forceinline__ long long qrw_clock_after(double x) {
   asm volatile("{ .reg .pred q; setp.ne.f64 q, %1, 0d7E37E43C8800759C; @q mov.u64 %0, %%clock64; }" : "+l"(t) : "d"(x) : "memory");
   return t;
 }
-__shared__ long long chain_stamp[8];  // probe build: clock at the five seams of the chain (lane 0)
-#endif
-QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, int lane) {
-#ifdef QRW_V2_TIMING
+__shared__ long long chain_stamp[8];  // probe build: clock at the five seams of the chain (lane 0 of E and of S)
 #define QRW_STAMP(n, x) { const long long t_ = qrw_clock_after(x); if (lane == 0) chain_stamp[n] = t_; }
 #else
 #define QRW_STAMP(n, x) ((void)0)
 #endif
+QRW_HDN void state_elim(const double* Sig, double* rec, int lane, unsigned tmr) {
   double lastv = (double)lane;  // what the probe build hangs its clock reads on
   QRW_STAMP(0, lastv);
   const int i0 = lane & 15;
@@ -409,34 +447,34 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
   // stage of this half at elimination step t: lower t, upper 15 - t
   const int k0 = (NS - 1) * upi;
   const int dk = 1 - 2 * upi;
-  double tc[2][12], sn;  // two column buffers: the prefetch must not wait for the registers of the column in use
+  cta::TRow tq[2];  // the column in flight; two buffers so that the request does not wait for the registers of the column in use
+  double sn;
+  cta::tmem_ld12(tmr, tq[0]);  // column i of T_0 / U_15
   {
     double* r0 = rec + SR * k0;
     double* r1 = rec + SR * (k0 + dk);
     const double p = r0[R_A + i] + r0[R_CC + i];
     if (wr) r0[R_SP + i] = p;
-    cta::lds12c<LD>(Tm + MS * (k0 - upi) + i, tc[0]);  // column i of T_0 / U_15
     sn = r1[R_A + i] + r1[R_CC + i];
   }
+  double tc[12];
 #pragma unroll
   for (int t = 0; t < 7; ++t) {
     const int kc = k0 + dk * t;  // stage whose s' is broadcast
     const int kn = kc + dk;      // stage produced
     double pv[12], sn2 = 0.0;
-    double* tn = tc[(t + 1) & 1];
     cta::wsync();
     if (t == 3) cta::nb_arrive(1, 64);  // s'_0..3 | s'_15..12 are in shared memory: the helper warp starts on their v_k
     if (t == 6) cta::nb_arrive(2, 64);  // s'_4..6 | s'_11..9
     cta::lds12(rec + SR * kc + R_SP, pv);
-    if (t < 6) {  // column i of T_k / U_k of the next step and its right-hand side
+    cta::tmem_get12(tq[t & 1], tc);
+    cta::tmem_ld12(tmr + 24 * (t + 1), tq[(t + 1) & 1]);  // column i of T_k / U_k of the next step (t = 6: of T_7 on every lane)
+    if (t < 6) {
       const double* r2 = rec + SR * (kn + dk);
-      cta::lds12c<LD>(Tm + MS * (kn - upi) + i, tn);
       sn2 = r2[R_A + i] + r2[R_CC + i];
-    } else {
-      cta::lds12c<LD>(Tm + MS * 7 + i, tn);  // the middle step: column i of T_7 on every lane
     }
     cta::sched_fence();
-    const double p = sub_dot12(sn, tc[t & 1], pv);
+    const double p = sub_dot12(sn, tc, pv);
     if (wr) rec[SR * kn + R_SP + i] = p;
     lastv = p;
     sn = sn2;
@@ -449,8 +487,9 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
     cta::wsync();
     cta::lds12(rec + SR * 7 + R_SP, pv);
     const double s8p = r8[R_SP + i];
+    cta::tmem_get12(tq[1], tc);
     cta::sched_fence();
-    const double s8 = sub_dot12(s8p, tc[1], pv);
+    const double s8 = sub_dot12(s8p, tc, pv);
     cta::wsync();  // everybody has read s'_8 before it is replaced by s''_8
     if (wr && !up) r8[R_SP + i] = s8;
     lastv = s8;
@@ -467,35 +506,49 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
     if (wr) rec[SR * kc + R_A + (R_XT - R_A) * upi + i] = v;
     lastv = v;
   }
+  cta::wsync();
+  cta::nb_arrive(4, 64);  // X_8 and v_7 are in shared memory: the back-substitution warp starts
   QRW_STAMP(3, lastv);
-  // ---- back-substitution: lower half stages 7..0, upper half stages 9..15 (idle in the last step)
-  double tr[2][12], vk;
-  cta::lds12(Tm + MS * (7 + upi) + LD * i, tr[0]);  // row i of T_7 / U_9
-  vk = 0.0;
+}
+
+// back-substitution: lower half stages 7..0, upper half stages 9..15 (idle in the last step):  X_k = v_k - T_k X_{k+1}
+QRW_HDN void state_back(double* rec, int lane, unsigned tmr) {
+  const int i0 = lane & 15;
+  int upi = lane >> 4;
+  cta::opaque(upi);
+  const bool up = upi != 0;
+  const int i = i0 < 12 ? i0 : 11;
+  const bool wr = i0 < 12;
+  const int k0 = (NS - 1) * upi;
+  const int dk = 1 - 2 * upi;
+  cta::TRow tq[2];
+  double tr[12], vk = 0.0, lastv = 0.0;
+  cta::tmem_ld12(tmr, tq[0]);  // row i of T_7 / U_9
+  cta::nb_sync(4, 64);         // the elimination warp has stored X_8 and v_7
 #pragma unroll
   for (int u = 0; u < 8; ++u) {
     const int kk = u < 7 ? 7 + 2 * upi - dk * u : k0;  // stage produced: 7 - u | 9 + u, the upper half repeats 15
     const int kp = kk + dk;                            // stage whose X is broadcast
     double xv[12], vn = 0.0;
-    double* tn = tr[(u + 1) & 1];
-    cta::wsync();
+    if (u > 0) cta::wsync();
     cta::lds12(rec + SR * kp + R_XT, xv);
+    cta::tmem_get12(tq[u & 1], tr);
     if (u < 7) {
       const int k2 = u < 6 ? 7 + 2 * upi - dk * (u + 1) : k0;
-      cta::lds12(Tm + MS * (k2 - upi) + LD * i, tn);  // row i of T_k / U_k of the next step
+      cta::tmem_ld12(tmr + 24 * (u + 1), tq[(u + 1) & 1]);  // row i of T_k / U_k of the next step
       if (u > 0) vn = rec[SR * k2 + R_A + i];
     }
     cta::sched_fence();
     double X;
     if (u == 0) {
       // the first step waits for the helper's v_k behind its product, not in front of it
-      const double d = dot12(tr[0], xv);
+      const double d = dot12(tr, xv);
       cta::nb_sync(3, 64);
       vk = rec[SR * kk + R_A + i];
       vn = rec[SR * (7 + 2 * upi - dk) + R_A + i];
       X = vk - d;
     } else {
-      X = sub_dot12(vk, tr[u & 1], xv);
+      X = sub_dot12(vk, tr, xv);
     }
     if (wr && (!up || u < 7)) rec[SR * kk + R_XT + i] = X;
     lastv = X;
@@ -504,10 +557,10 @@ QRW_HDN void state_recurrence(const double* Sig, const double* Tm, double* rec, 
   QRW_STAMP(4, lastv);
 }
 
-// The helper warp (the warp next to the chain warp, idle otherwise): v_k = Sig_k s'_k for k = 0..6 (lower half) and 15..9
-// (upper half), parked in the A slot of the stage, in two groups behind the elimination (named barriers 1 and 2); barrier
-// 3 hands them to the back-substitution.  Seven independent products, double-buffered.
-QRW_HDN void state_helper(const double* Sig, double* rec, int lane) {
+// The helper warp: v_k = Sig_k s'_k for k = 0..6 (lower half) and 15..9 (upper half), parked in the A slot of the stage, in
+// two groups behind the elimination (named barriers 1 and 2); barrier 3 hands them to the back-substitution.  Seven
+// independent products; the Sig rows come from tensor memory, one request in flight.
+QRW_HDN void state_helper(double* rec, int lane, unsigned tmr) {
   const int i0 = lane & 15;
   int upi = lane >> 4;
   cta::opaque(upi);
@@ -515,20 +568,22 @@ QRW_HDN void state_helper(const double* Sig, double* rec, int lane) {
   const bool wr = i0 < 12;
   const int k0 = (NS - 1) * upi;
   const int dk = 1 - 2 * upi;
-  double sg[2][12], pv[2][12];
-  cta::lds12(Sig + MS * k0 + LD * i, sg[0]);
+  cta::TRow tq[2];
+  double sg[12], pv[2][12];
+  cta::tmem_ld12(tmr, tq[0]);
   cta::nb_sync(1, 64);
   cta::lds12(rec + SR * k0 + R_SP, pv[0]);
 #pragma unroll
   for (int t = 0; t < 7; ++t) {
     const int kc = k0 + dk * t;
+    cta::tmem_get12(tq[t & 1], sg);
     if (t < 6) {
       const int k2 = kc + dk;
-      cta::lds12(Sig + MS * k2 + LD * i, sg[(t + 1) & 1]);
+      cta::tmem_ld12(tmr + 24 * (t + 1), tq[(t + 1) & 1]);
       if (t == 3) cta::nb_sync(2, 64);
       cta::lds12(rec + SR * k2 + R_SP, pv[(t + 1) & 1]);
     }
-    const double v = dot12(sg[t & 1], pv[t & 1]);
+    const double v = dot12(sg, pv[t & 1]);
     if (wr) rec[SR * kc + R_A + i] = v;
   }
   cta::wsync();
@@ -537,11 +592,14 @@ QRW_HDN void state_helper(const double* Sig, double* rec, int lane) {
 
 // ------------------------------------------------------------------------------------------
 // One full MPC::run for one instance; every thread of the CTA calls it with the same arguments.
-// Same I/O contract as mpc_solve_instance (mpc_core.cuh).  recw = the warp that runs the recurrences.
+// Same I/O contract as mpc_solve_instance (mpc_core.cuh).  recw = the first of the three warps that run the state chain
+// (elimination, helper, back-substitution on warps recw, recw + 1, recw + 2: three different lane quadrants of tensor
+// memory); tmem = base address of the CTA's tensor-memory allocation (cta::TMEM_COLS columns).
 // ------------------------------------------------------------------------------------------
 QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, const double* fs, double* st_d,
-                         int* st_i, int first, double* out, int* info, double* rho_out, double* dbg, int recw) {
+                         int* st_i, int first, double* out, int* info, double* rho_out, double* dbg, int recw, unsigned tmem) {
   const Sm S(slab);
+  const unsigned tm = cta::tmem_addr(tmem, 0);  // this thread's lane quadrant
 #ifdef QRW_V2_TIMING
   const long long t_entry = qrw_clock();
 #endif
@@ -840,7 +898,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
 #ifdef QRW_V2_TIMING
       const long long tF = qrw_clock();
 #endif
-      factor(C, S, R, Rh, S.red[120], tid);
+      factor(C, S, R, Rh, S.red[120], tid, recw, tm);
       QRW_TICK(6, tF);
 #ifdef QRW_V2_TIMING
       tA = qrw_clock();
@@ -864,6 +922,9 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
 #ifdef QRW_V2_TIMING
     tp[0] += qrw_clock() - tL, tL = qrw_clock();
 #endif
+    // row j of F_k^-1 from the thread's tensor-memory lane: requested here, needed in phase (3)
+    cta::TRow tfi;
+    cta::tmem_ld12(tm + TM_FI + 24 * (w >> 2), tfi);
     // (2) t_f = sigma x_f + D_f (A' u)_f
     if (isv) {
       double v = C.dtm * BAk[6 + c3];
@@ -884,12 +945,13 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
     // (3) u_f = F^-1 t_f and w = GF t_f (rows 6..11) from the same broadcast of t_f;
     //     m = u - rho E w: what the state system sees of the dynamics rows; A_k = sigma x_X - D_X m_k
     double uf = 0.0, wv = 0.0, mk = 0.0;
+    double fv[12];
+    cta::tmem_get12(tfi, fv);  // warp-uniform (tcgen05.wait::ld is warp-collective): outside the lane branch
     if (isv) {
-      // rows of F^-1 and GF as six LDS.128 each, issued back to back with the broadcast of t_f: left to itself ptxas
-      // loaded them one LDS.64 at a time right in front of the FMA that uses it (a shared-memory latency per product)
-      double tv[12], fv[12];
+      // row of GF as six LDS.128, issued back to back with the broadcast of t_f: left to itself ptxas loaded it one
+      // LDS.64 at a time right in front of the FMA that uses it (a shared-memory latency per product)
+      double tv[12];
       cta::lds12(BBk, tv);
-      cta::lds12(rec + R_FI + LD * j, fv);  // (no warp fence here: lanes 12..15 of a stage are not in this branch)
       double gv[12];  // lanes j < 6 have no GF row: they read the (valid, aligned) words in front of it and drop the product
       cta::lds12(rec + R_GF + LD * (j - 6), gv);
       uf = dot12a(fv, tv);
@@ -919,18 +981,16 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
 #endif
     // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
     // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
-    if (w == recw) state_recurrence(S.Sig, S.T, S.rec, l);
-    else if (w == ((recw + 1) & 7)) state_helper(S.Sig, S.rec, l);
-#ifdef QRW_V2_TIMING
-    if (w == recw) {
-      QRW_TICK(4, tA);
-      cta::wsync();
-      const volatile long long* cs = chain_stamp;
-      for (int q = 0; q < 4; ++q) tcs[q] += cs[q + 1] - cs[q];
-    }
-#endif
+    if (w == recw) state_elim(S.Sig, S.rec, l, tm + TM_ROLE);
+    else if (w == ((recw + 1) & 7)) state_helper(S.rec, l, tm + TM_ROLE);
+    else if (w == ((recw + 2) & 7)) state_back(S.rec, l, tm + TM_ROLE);
     cta::bar();
 #ifdef QRW_V2_TIMING
+    if (w == recw) {  // the stamps of the elimination (0..3) and of the back-substitution warp (4) are complete behind the barrier
+      const volatile long long* cs = chain_stamp;
+      tq[4] += cs[4] - cs[0];
+      for (int q = 0; q < 4; ++q) tcs[q] += cs[q + 1] - cs[q];
+    }
     tA = qrw_clock();
     tL = tA;
 #endif

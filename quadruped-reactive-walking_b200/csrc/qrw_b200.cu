@@ -98,6 +98,8 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
   extern __shared__ __align__(16) double slab[];
   int* next = reinterpret_cast<int*>(slab + v2::V_INT) + 127;
   const int recw = (blockIdx.x / sms) & 3;
+  // 256 of the SM's 512 tensor-memory columns for the whole life of this (persistent) CTA: the matrix rows of the solve
+  const unsigned tmem = cta::tmem_alloc(reinterpret_cast<unsigned*>(slab + v2::V_INT) + v2::V2_TMEM_SLOT);
   for (;;) {
     if (threadIdx.x == 0) {
       const int idx = atomicAdd(counter, 1);
@@ -117,9 +119,10 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
     }
     v2::mpc_v2_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
                      st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, f,
-                     out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw);
+                     out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw, tmem);
     __syncthreads();
   }
+  cta::tmem_free(tmem);
 }
 
 // Work order of the next launch: robots sorted by the ADMM iteration count of their previous solve, longest first

@@ -119,6 +119,72 @@ __device__ __forceinline__ void opaque(int& v) { asm volatile("" : "+r"(v)); }
 // Scheduling fence for ptxas: a warp barrier is never crossed by its instruction scheduler, so the loads issued
 // before it stay grouped ahead of the arithmetic that follows (costs one issue slot).
 __device__ __forceinline__ void sched_fence() { __syncwarp(); }
+// ------------------------------------------------------------------------------------------
+// Tensor memory (TMEM, 256 KB per SM next to the tensor cores) used as a PER-LANE scratchpad for matrix rows -- no
+// tcgen05.mma involved.  tcgen05.ld/st.32x32b: thread t of warp w reads/writes consecutive 32-bit columns of TMEM lane
+// 32 (w % 4) + t, so a row a lane reads again in every ADMM iteration can live there instead of in shared memory.
+// Measured on B200 (tools/tmem_bench.cu, profiles/r02_tmem_bench.txt): dependent load 34 cycles (LDS 29), 840 B/cycle/SM
+// (shared memory 128), and -- the point -- TMEM loads neither queue behind shared-memory traffic nor delay it
+// (LDS latency under an LDS.128 stream of the other warps: 163 cycles; under a tcgen05.ld stream: 30).
+// Addresses: bits 31..16 lane, bits 15..0 column.  Everything here is warp-collective (.sync.aligned): call it from
+// warp-uniform code only.  A row = 12 doubles = 24 columns = one x16 + one x8 access.
+// ------------------------------------------------------------------------------------------
+constexpr int TMEM_COLS = 256;  // columns a CTA allocates: two CTAs per SM share the 512
+// whole CTA calls it (it ends with a CTA barrier); warp 0 allocates.  Returns the base address.
+__device__ __forceinline__ unsigned tmem_alloc(unsigned* slot) {
+  if (threadIdx.x < 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  return *slot;
+}
+__device__ __forceinline__ void tmem_free(unsigned base) {
+  __syncthreads();
+  if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "r"(TMEM_COLS) : "memory");
+}
+// address of column `col` in the calling warp's lane quadrant
+__device__ __forceinline__ unsigned tmem_addr(unsigned base, int col) { return base + ((unsigned)(threadIdx.x & 96) << 16) + (unsigned)col; }
+struct TRow {
+  unsigned r[24];
+};
+// request the 12 doubles at `addr` (asynchronous; tmem_get12 waits)
+__device__ __forceinline__ void tmem_ld12(unsigned addr, TRow& t) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(t.r[0]), "=r"(t.r[1]), "=r"(t.r[2]), "=r"(t.r[3]), "=r"(t.r[4]), "=r"(t.r[5]), "=r"(t.r[6]), "=r"(t.r[7]),
+                 "=r"(t.r[8]), "=r"(t.r[9]), "=r"(t.r[10]), "=r"(t.r[11]), "=r"(t.r[12]), "=r"(t.r[13]), "=r"(t.r[14]), "=r"(t.r[15])
+               : "r"(addr));
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(t.r[16]), "=r"(t.r[17]), "=r"(t.r[18]), "=r"(t.r[19]), "=r"(t.r[20]), "=r"(t.r[21]), "=r"(t.r[22]), "=r"(t.r[23])
+               : "r"(addr + 16));
+}
+// wait for every outstanding tcgen05.ld of the thread, then hand the row out as doubles.  The registers are in/out
+// operands of the wait so that the compiler cannot move a use in front of it.
+__device__ __forceinline__ void tmem_get12(TRow& t, double* v) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(t.r[0]), "+r"(t.r[1]), "+r"(t.r[2]), "+r"(t.r[3]), "+r"(t.r[4]), "+r"(t.r[5]), "+r"(t.r[6]), "+r"(t.r[7]),
+                 "+r"(t.r[8]), "+r"(t.r[9]), "+r"(t.r[10]), "+r"(t.r[11]), "+r"(t.r[12]), "+r"(t.r[13]), "+r"(t.r[14]), "+r"(t.r[15]),
+                 "+r"(t.r[16]), "+r"(t.r[17]), "+r"(t.r[18]), "+r"(t.r[19]), "+r"(t.r[20]), "+r"(t.r[21]), "+r"(t.r[22]), "+r"(t.r[23])
+               :
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 12; ++i) v[i] = __hiloint2double((int)t.r[2 * i + 1], (int)t.r[2 * i]);
+}
+__device__ __forceinline__ void tmem_st12(unsigned addr, const double* v) {
+  unsigned r[24];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) r[2 * i] = (unsigned)__double2loint(v[i]), r[2 * i + 1] = (unsigned)__double2hiint(v[i]);
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(addr),
+               "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+               "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+               : "memory");
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(addr + 16), "r"(r[16]), "r"(r[17]),
+               "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 }  // namespace cta
 }  // namespace qrw
 #else
@@ -147,6 +213,18 @@ template <int STRIDE>
 inline void lds12c(const double* p, double* v) {
   for (int i = 0; i < 12; ++i) v[i] = p[STRIDE * i];
 }
+// tensor-memory scratchpad: tests/emu/cta_emu.hpp keeps one array per emulated CTA, private to (lane quadrant, lane)
+constexpr int TMEM_COLS = 256;
+struct TRow {
+  double d[12];
+};
+unsigned tmem_addr(unsigned base, int col);
+void tmem_ld12(unsigned addr, TRow& t);
+inline void tmem_get12(TRow& t, double* v) {
+  for (int i = 0; i < 12; ++i) v[i] = t.d[i];
+}
+void tmem_st12(unsigned addr, const double* v);
+inline void tmem_wait_st() {}
 }  // namespace cta
 }  // namespace qrw
 #endif

@@ -10,6 +10,8 @@
 #include <functional>
 #include <vector>
 
+#include "../../quadruped-reactive-walking_b200/csrc/qrw_spmd.cuh"  // declarations of the qrw::cta primitives defined here (TRow)
+
 #if !defined(__x86_64__)
 #error "cta_emu.hpp: x86-64 only"
 #endif
@@ -50,6 +52,7 @@ struct Emu {
   std::vector<char*> stacks;
   std::vector<int> state;
   std::vector<double> xch;
+  std::vector<double> tmem = std::vector<double>(128 * 128, 0.0);  // tensor memory of the CTA: 128 lanes x 256 columns (128 doubles)
   void* sched_sp = nullptr;
   std::function<void()> body;
   static constexpr size_t STACK = 256 * 1024;
@@ -209,6 +212,25 @@ inline double shfl_xor(double v, int m) {
   const double r = e->xch[(t & ~31) + ((t ^ m) & 31)];
   wsync();
   return r;
+}
+// tensor memory: a thread reaches the lane (warp % 4) * 32 + lane of its quadrant and nothing else
+inline unsigned tmem_addr(unsigned base, int col) { return base + ((unsigned)(g_emu->cur & 96) << 16) + (unsigned)col; }
+inline double* tmem_row(unsigned addr) {
+  Emu* e = g_emu;
+  const int lane0 = (int)(addr >> 16), col = (int)(addr & 0xffff);
+  if (lane0 != (e->cur & 96) || (col & 1) || col + 24 > 256) {
+    fprintf(stderr, "cta_emu: bad TMEM access by thread %d (lane base %d, column %d)\n", e->cur, lane0, col);
+    abort();
+  }
+  return e->tmem.data() + (size_t)(lane0 + (e->cur & 31)) * 128 + col / 2;
+}
+inline void tmem_ld12(unsigned addr, TRow& t) {
+  const double* p = tmem_row(addr);
+  for (int i = 0; i < 12; ++i) t.d[i] = p[i];
+}
+inline void tmem_st12(unsigned addr, const double* v) {
+  double* p = tmem_row(addr);
+  for (int i = 0; i < 12; ++i) p[i] = v[i];
 }
 inline int fetch_add(int* p, int v) {
   const int o = *p;

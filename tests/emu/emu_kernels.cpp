@@ -118,7 +118,7 @@ extern "C" void emu_mpc_v2_run(int B, double dt, int N_gait, int first, int max_
       cta::run_cta(v2::NT, [&]() {
         v2::mpc_v2_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
                          st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
-                         out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8);
+                         out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8, 0u);
       });
     }
     if (nthreads <= 1) g_last_slab = slab;

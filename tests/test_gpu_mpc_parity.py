@@ -237,3 +237,85 @@ def test_config3_full_size_mixed_gaits_sampled_against_oracle(oracle):
         swing = w.gait(t)[:, :16] == 0
         assert np.abs(f[ok][swing[ok]]).max() < 1e-3
         x0 = rg[:, :12].copy()
+
+
+def test_bench_history_sampled_against_oracle(oracle):
+    """The history bench.py times -- MpcWorkload(4096, seed 1): tick 0 cold, then 25 warm-started update ticks in closed
+    loop (reference src/MPC.cpp:509-558: warm start and rho persist between calls; state advance as scripts/test_mpc.py:78)
+    -- with 256 sampled robots re-solved by the oracle on the same inputs.  ADMM terminates on a 25-iteration grid
+    (check_termination), so on a long history a round-off-sized difference can move a robot's stop by one check; the test
+    counts those flips and bounds the force difference when one happens instead of pretending there are none."""
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B, T, NS_ = 4096, 25, 256
+    w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=T + 2)
+    idx = np.random.default_rng(0).choice(B, NS_, replace=False)
+    idx.sort()
+    gpu, cpu = BatchedMPC(B), oracle.OracleMPC(NS_)
+    x0 = None
+    flips, n_rt, worst_same, worst_flip = 0, 0, 0.0, 0.0
+    flipped_ever = np.zeros(NS_, bool)
+    for t in range(T + 1):
+        xr, fs = w.inputs(t, x0)
+        gpu.run(t, xr, fs)
+        cpu.run(t, xr[idx], fs[idx], 16)
+        rg, rc = gpu.get_latest_result(), cpu.get_latest_result()
+        assert np.array_equal(gpu.get_gait()[idx], cpu.get_gait()) and np.array_equal(gpu.get_Sgait()[idx], cpu.get_Sgait())
+        same = gpu.info()["iters"][idx] == cpu.info()["iters"]
+        flipped_ever |= ~same
+        clean = ~flipped_ever  # robots whose whole history so far stopped at the same checks as the oracle's
+        err = np.abs(rg[idx] - rc)
+        tol = 1e-4 + 1e-5 * np.abs(rc)
+        assert (err[clean] <= tol[clean]).all(), f"tick {t}: {np.abs(err[clean]).max():.3e} on a robot with identical iteration counts"
+        worst_same = max(worst_same, err[clean].max() if clean.any() else 0.0)
+        if (~clean).any():
+            worst_flip = max(worst_flip, err[~clean].reshape(-1, 16, 24)[:, :, 12:].max())
+        flips += int((~same).sum())
+        n_rt += NS_
+        x0 = rg[:, :12].copy()  # the GPU's own closed loop, as bench.py runs it
+    print(f"bench history: {flips} of {n_rt} robot-ticks stopped at a different check than the oracle ({flipped_ever.sum()} of {NS_} robots "
+          f"at least once); max |diff| {worst_same:.2e} on identical histories, {worst_flip:.2e} N on forces after a flip")
+    # a flip is one extra (or one fewer) batch of 25 iterations near convergence: the result moves by less than the
+    # stopping tolerance allows; the robot then carries a different warm start, so later ticks of it are not compared bit-wise
+    assert flipped_ever.mean() <= 0.05, "more than 5 % of the sampled robots left the oracle's iteration counts"
+    assert worst_flip < 2e-2, "force difference after an iteration-count flip exceeds the distance-to-optimum bound (tests/test_exact_qp.py)"
+
+
+@pytest.mark.parametrize("trot,offset,n_calls,atol", [(False, False, 100, 1e-3), (False, True, 500, 1e-3), (True, False, 500, 1e-2)])
+def test_reference_scenarios_on_the_gpu(trot, offset, n_calls, atol):
+    """scripts/test_mpc.py:54-160 (four-stance immobile / offset, trot centred) with the reference's call counts and its
+    own assertions, through the drop-in module's MPC class on the CUDA kernel."""
+    import libquadruped_reactive_walking as lqrw
+    from test_reference_scripts import run_scenario
+
+    m = lqrw.MPC(0.02, 16, 0.32, 20)
+
+    def solve(i, xref, fsteps, gait):
+        m.run(i, xref, fsteps)
+        return m.get_latest_result()
+
+    x_f, xref = run_scenario(solve, n_calls, trot, offset)
+    if not trot:
+        assert np.allclose(x_f[12:, 0], np.array([x_f[12, 0], x_f[13, 0], x_f[14, 0]] * 4)), "All feet forces are equal."
+    assert np.allclose(x_f[:12, 0], xref[:, 1], atol=atol), "Close to reference state"
+
+
+def test_reference_offset_trot_scenario_on_the_gpu_follows_the_oracle(oracle):
+    """scripts/test_mpc.py:162-190: the scenario whose assertion does not hold for this QP (see
+    tests/test_reference_scripts.py): the CUDA kernel follows the oracle call by call while the loop is in its bounded phase."""
+    import libquadruped_reactive_walking as lqrw
+    from test_reference_scripts import run_scenario
+
+    m, o = lqrw.MPC(0.02, 16, 0.32, 20), oracle.OracleMPC(1)
+    calls = []
+
+    def solve(i, xref, fsteps, gait):
+        m.run(i, xref, fsteps)
+        o.run(i, xref.ravel(order="F")[None, :], fsteps.ravel(order="F")[None, :])
+        rg, ro = m.get_latest_result(), o.get_latest_result().reshape(16, 24).T
+        assert_forces_close(rg, ro, f"call {i}")
+        calls.append(i)
+        return ro
+
+    run_scenario(solve, 60, True, True)
+    assert len(calls) == 60
