@@ -45,13 +45,21 @@ int qrw_fp64_peak(int device, double* tflops);
  * MPC -- replaces class MPC (include/qrw/MPC.hpp:16-129, src/MPC.cpp)
  * ------------------------------------------------------------------------------------- */
 /* MPC::MPC(dt, n_steps, T_gait, N_gait), src/MPC.cpp:3-32, for `batch` robots on `device`.
- * Only the reference configuration n_steps == 16 is compiled in (src/config_solo12.yaml:11-13);
- * n_steps < N_gait <= 32. */
+ * LIMIT: only the reference configuration n_steps == 16 (T_mpc / dt_mpc = 0.32 / 0.02, src/config_solo12.yaml:11-13)
+ * is compiled in -- the kernels map one horizon stage to 16 lanes of a 256-thread CTA; any other value fails with a
+ * message naming the limit.  n_steps < N_gait <= 32. */
 int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_gait, int N_gait, int device);
 int qrw_mpc_destroy(qrw_mpc_t* h);
 /* MPC::run(num_iter, xref_in, fsteps_in), src/MPC.cpp:626-649.  num_iter == 0 takes the
  * create_matrices/osqp_setup path (cold start), anything else the update path (warm start from
- * the state left by the previous call).  One value for the whole batch. */
+ * the state left by the previous call).  One value for the whole batch.
+ * STREAM CONTRACT: _device entry points are asynchronous on the caller's `stream`.  Every launch is followed by an
+ * event on that stream, and qrw_mpc_result_host / qrw_mpc_gait_host / qrw_mpc_sgait_host wait for the event of the
+ * LAST launch before they copy (they block the host until the copy is done), so run_device(...) followed by
+ * result_host(...) needs no synchronisation by the caller.  qrw_mpc_info_host and the debug / wbc / wbctick host
+ * getters synchronise the whole device.  Exception: a launch captured into a CUDA graph records no event -- callers
+ * that replay graphs synchronise the replay stream themselves.  qrw_mpc_result_device only returns a pointer: reading
+ * it is ordered by the caller's own stream. */
 int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const double* d_fsteps, void* stream);
 int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const double* fsteps);
 /* MPC::run with a per-robot call index d_k [B] (device ints): < 0 = robot not called in this launch (solver state and
@@ -71,9 +79,10 @@ int qrw_mpc_info_host(qrw_mpc_t* h, int* iters, int* status, double* rho, int* n
  * (D[384] | E[704] | c | unscaled dynamics bounds[192]) of every instance after the next run */
 int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter);
 int qrw_mpc_debug_host(qrw_mpc_t* h, double* out /* [B][1281] */);
-/* which CUDA kernel runs the solve: 1 (default) = one 256-thread CTA per instance (mpc_cta_core.cuh),
- * 0 = one warp per instance (mpc_core.cuh, the round-1 v0 kernel kept for A/B checks).  Both carry the
- * same persistent state and follow the same OSQP iterate sequence. */
+/* which CUDA kernel runs the solve: 2 (default) = force-first elimination, one 256-thread CTA per instance, matrix rows in
+ * tensor memory (mpc_v2_core.cuh); 1 = 24x24 block-tridiagonal CTA kernel (mpc_cta_core.cuh); 0 = one warp per instance
+ * (mpc_core.cuh).  1 and 0 are the superseded round-1 kernels kept for A/B parity checks.  All three carry the same
+ * persistent state and follow the same OSQP iterate sequence. */
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant);
 /* work order of the persistent grid (default kernel): 0 (default) = index order; 1 = robots sorted by the ADMM iteration
  * count of their previous solve, longest first (measured on B200: no gain, kept as an A/B hook).  Results do not depend

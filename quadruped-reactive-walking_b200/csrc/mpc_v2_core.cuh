@@ -75,7 +75,9 @@ static_assert(TM_ROLE + 8 * 24 <= cta::TMEM_COLS, "tensor-memory columns of a CT
 constexpr int V_W = V_REC + 16 * SR;  // [144] Gauss-Jordan ping-pong / T_k staging of the factorisation
 constexpr int V_RED = V_W + 144;      // 128   reductions
 constexpr int V_INT = V_RED + 128;    // 128 ints
-constexpr int V2_SLAB_DOUBLES = V_INT + 64;
+constexpr int V_PARK = V_INT + 64;    // [3][32][PK] solver state of the three chain warps while they run the chain
+constexpr int PK = 18;                // 16 doubles per lane, padded so that the lanes' 16-byte accesses fall on distinct banks
+constexpr int V2_SLAB_DOUBLES = V_PARK + 3 * 32 * PK;
 constexpr int V2_SLAB_BYTES = V2_SLAB_DOUBLES * 8;
 // factorisation scratch inside a record, aliased on the iteration-only vectors [0, 112)
 constexpr int R_Y = 0;   // [12][6] F_k^-1 (D_f B0')(:, rows 6..11); dead after step (c)
@@ -86,10 +88,10 @@ static_assert(V2_SLAB_BYTES <= 112 * 1024, "two CTAs per SM need <= 113 KB each"
 constexpr int V2_TMEM_SLOT = 120;  // index in the int buffer where tcgen05.alloc parks the CTA's tensor-memory base address
 
 struct Sm {
-  double *Sig, *T, *rec, *W, *red;
+  double *Sig, *T, *rec, *W, *red, *park;
   int* ib;
   QRW_HD explicit Sm(double* b)
-      : Sig(b + V_SIG), T(b + V_T), rec(b + V_REC), W(b + V_W), red(b + V_RED),
+      : Sig(b + V_SIG), T(b + V_T), rec(b + V_REC), W(b + V_W), red(b + V_RED), park(b + V_PARK),
         ib(reinterpret_cast<int*>(b + V_INT)) {}
 };
 
@@ -979,11 +981,21 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
 #ifdef QRW_V2_TIMING
     tA = qrw_clock();
 #endif
-    // the chain is a real call (noinline): its ~100 registers then do not compete with the solver state every
-    // thread keeps live across it (inlined, ptxas spilled F^-1 to local memory for ALL warps, r01 ncu)
-    if (w == recw) state_elim(S.Sig, S.rec, l, tm + TM_ROLE);
-    else if (w == ((recw + 1) & 7)) state_helper(S.rec, l, tm + TM_ROLE);
-    else if (w == ((recw + 2) & 7)) state_back(S.rec, l, tm + TM_ROLE);
+    // The chain is a real call (noinline).  ptxas gives a callee the registers that are dead at the call site; with the
+    // solver state of the calling thread live across it that left ~60, and the chain serialised its six broadcast loads
+    // behind the FMAs for want of 12 more (SASS of r02c: one LDS.128 latency per pair of products, 170-220 cycles per
+    // step against ~100).  The three chain warps therefore park their iterates in shared memory around the call.
+    const int role = (w - recw) & 7;
+    if (role < 3) {
+      double* pk = S.park + (32 * role + l) * PK;
+      pk[0] = R.xf, pk[1] = R.xX, pk[2] = R.dF, pk[3] = R.dX, pk[4] = R.z1, pk[5] = R.y1, pk[6] = R.e1, pk[7] = R.y2;
+      pk[8] = R.zA, pk[9] = R.yA, pk[10] = R.eA, pk[11] = R.zB, pk[12] = R.yB, pk[13] = R.eB, pk[14] = uf, pk[15] = wv;
+      if (role == 0) state_elim(S.Sig, S.rec, l, tm + TM_ROLE);
+      else if (role == 1) state_helper(S.rec, l, tm + TM_ROLE);
+      else state_back(S.rec, l, tm + TM_ROLE);
+      R.xf = pk[0], R.xX = pk[1], R.dF = pk[2], R.dX = pk[3], R.z1 = pk[4], R.y1 = pk[5], R.e1 = pk[6], R.y2 = pk[7];
+      R.zA = pk[8], R.yA = pk[9], R.eA = pk[10], R.zB = pk[11], R.yB = pk[12], R.eB = pk[13], uf = pk[14], wv = pk[15];
+    }
     cta::bar();
 #ifdef QRW_V2_TIMING
     if (w == recw) {  // the stamps of the elimination (0..3) and of the back-substitution warp (4) are complete behind the barrier

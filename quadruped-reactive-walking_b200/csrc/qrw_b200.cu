@@ -5,10 +5,10 @@
 //        -Xcompiler -fPIC -o libqrw_b200.so qrw_b200.cu
 // Plain CUDA runtime only -- no torch, no cuBLAS.  There is no CPU fallback in this library.
 //
-// Execution model: a persistent grid of one-warp CTAs (three per SM for the MPC: each owns a
-// 75 KB shared-memory slab holding one instance's whole solver state) pulls instance indices
-// from a global work counter, so the large spread of ADMM iteration counts across a batch
-// (25 ... 4000) does not leave SMs idle behind a slow instance.
+// Execution model of the MPC (mpc_v2_kernel): a persistent grid of 256-thread CTAs, two per SM (128 registers, 89 KB of
+// shared memory and 256 tensor-memory columns each), one robot per CTA at a time; CTAs pull robot indices from a global
+// work counter, so the large spread of ADMM iteration counts across a batch (25 ... 4000) does not leave SMs idle
+// behind a slow robot.  The two round-1 kernels (warp per robot, 24x24 block CTA) stay selectable for A/B parity runs.
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -431,6 +431,17 @@ __global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, 
   out[blockIdx.x * blockDim.x + threadIdx.x] = ((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7));
 }
 
+// Event behind a launch on the caller's stream, for host getters that copy on the handle's private stream.  Skipped while
+// the stream is being captured into a CUDA graph (an event recorded there belongs to the capture): callers that replay
+// graphs synchronise the replay stream themselves before reading results.
+int record_done(cudaEvent_t ev, cudaStream_t s) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &st) != cudaSuccess) return fail("cudaStreamIsCapturing failed");
+  if (st != cudaStreamCaptureStatusNone) return 0;
+  CU(cudaEventRecord(ev, s));
+  return 0;
+}
+
 int sm_count_of(int device) {
   int n = 0;
   if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
@@ -453,6 +464,7 @@ struct qrw_mpc {
   bool use_order = false;  // measured on B200: no gain (40.7 vs 40.0 ms per 4096-robot step), see DESIGN.md 4.1
   double *h_xref = nullptr, *h_fsteps = nullptr, *h_out = nullptr;  // pinned
   cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;  // recorded behind every solve launch on the CALLER's stream; the host getters wait for it
 };
 struct qrw_wbc {
   int B, device, sms;
@@ -545,7 +557,10 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   (void)T_gait;  // stored by the reference (MPC.cpp:6) but never read on this path
   if (!out) return fail("qrw_mpc_create: null output handle");
   if (batch <= 0) return fail("qrw_mpc_create: batch must be positive");
-  if (n_steps != NS) return fail("qrw_mpc_create: only n_steps == 16 is compiled in (src/config_solo12.yaml)");
+  if (n_steps != NS)
+    return fail("qrw_mpc_create: n_steps = " + std::to_string(n_steps) +
+                " is not supported: this library compiles the reference configuration n_steps == 16 only "
+                "(T_mpc / dt_mpc = 0.32 / 0.02, src/config_solo12.yaml:11-13; one horizon stage per 16 lanes of a 256-thread CTA)");
   if (N_gait <= n_steps || N_gait > NGMAX)
     return fail("qrw_mpc_create: need n_steps < N_gait <= 32 (the reference writes gait.row(n_active))");
   int ndev = 0;
@@ -581,6 +596,7 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CU(cudaMallocHost(&h->h_fsteps, B * 12 * N_gait * sizeof(double)));
   CU(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)));
   CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming));
   CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
@@ -606,6 +622,7 @@ int qrw_mpc_destroy(qrw_mpc_t* h) {
   cudaFreeHost(h->h_xref);
   cudaFreeHost(h->h_fsteps);
   cudaFreeHost(h->h_out);
+  if (h->done) cudaEventDestroy(h->done);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return 0;
@@ -644,7 +661,7 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   }
   ++g_launches;
   CU(cudaGetLastError());
-  return 0;
+  return record_done(h->done, s);  // qrw_mpc_result_host / gait_host / sgait_host order themselves behind this launch
 }
 
 // MPC::run with a PER-ROBOT call index: d_k[b] < 0 -> robot b is not called in this launch (its solver state and its
@@ -663,7 +680,7 @@ int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xre
                                                         nullptr);
   ++g_launches;
   CU(cudaGetLastError());
-  return 0;
+  return record_done(h->done, s);
 }
 
 // A/B hook: 0 (default) = robots are taken in index order, 1 = longest-expected-solve first (mpc_order_kernel)
@@ -687,6 +704,7 @@ int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const doubl
 int qrw_mpc_result_host(qrw_mpc_t* h, double* out) {
   if (!h || !out) return fail("qrw_mpc_result_host: null argument");
   CU(cudaSetDevice(h->device));
+  CU(cudaStreamWaitEvent(h->stream, h->done, 0));  // the last solve may have been launched on another stream
   CU(cudaMemcpyAsync(out, h->d_out, (size_t)h->B * 24 * NS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   return 0;
@@ -698,6 +716,7 @@ int qrw_mpc_result_device(qrw_mpc_t* h, const double** d_out) {
 }
 
 static int mpc_unpack(qrw_mpc_t* h) {
+  CU(cudaStreamWaitEvent(h->stream, h->done, 0));
   const int per = 4 * h->N_gait + 12 * NS;
   const long long total = (long long)h->B * per;
   mpc_unpack_gait_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(h->d_state_i, h->B, h->N_gait,

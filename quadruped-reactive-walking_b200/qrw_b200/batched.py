@@ -129,7 +129,7 @@ class BatchedMPC:
         check(self._L.qrw_mpc_set_max_iter(self._h, int(k)))
 
     def set_kernel(self, variant):
-        """1 = CTA per instance (default), 0 = warp per instance (v0)."""
+        """2 = force-first CTA kernel with tensor-memory rows (default), 1 = v1 CTA kernel, 0 = warp per instance (v0)."""
         check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
 
     def set_work_order(self, longest_first):
