@@ -19,6 +19,7 @@
 #include "mpc_core.cuh"
 #include "mpc_cta_core.cuh"
 #include "mpc_v2_core.cuh"
+#include "mpc_v3_core.cuh"
 #include "wbc_core.cuh"
 #include "solo12_core.cuh"
 
@@ -120,6 +121,42 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
     v2::mpc_v2_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
                      st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, f,
                      out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw, tmem);
+    __syncthreads();
+  }
+  cta::tmem_free(tmem);
+}
+
+// Nested-dissection CTA-per-instance MPC solve (mpc_v3_core.cuh, the default): persistent grid of 256-thread CTAs, two per
+// SM (128 registers per thread, 113 KB of shared memory and 256 tensor-memory columns each), pulling instance indices
+// from the global work counter.
+__global__ void __launch_bounds__(nd::NT, 2) mpc_v3_kernel(const MpcConst C, const int B, const int first,
+                                                           const double* __restrict__ xref,
+                                                           const double* __restrict__ fsteps, double* st_d,
+                                                           int* st_i, double* out, int* info, double* rho,
+                                                           double* dbg, int* counter, const int* __restrict__ k_arr,
+                                                           const int* __restrict__ order) {
+  extern __shared__ __align__(16) double slab[];
+  int* next = reinterpret_cast<int*>(slab + nd::V_INT) + 127;
+  // 256 of the SM's 512 tensor-memory columns for the whole life of this (persistent) CTA: the matrix rows of the solve
+  const unsigned tmem = cta::tmem_alloc(reinterpret_cast<unsigned*>(slab + nd::V_INT) + nd::V3_TMEM_SLOT);
+  for (;;) {
+    if (threadIdx.x == 0) {
+      const int idx = atomicAdd(counter, 1);
+      *next = idx < B ? (order ? order[idx] : idx) : B;  // longest-expected solves first (mpc_order_kernel)
+    }
+    __syncthreads();
+    const int b = *next;
+    if (b >= B) break;
+    int f = first;
+    if (k_arr) {  // per-instance call index (qrw_mpc_run_indexed_device): < 0 = no call for this robot in this launch
+      const int kb = k_arr[b];
+      if (kb < 0) {
+        __syncthreads();
+        continue;
+      }
+      f = kb == 0 ? 1 : 0;
+    }
+    nd::mpc_v3_solve(C, slab, nd::MpcIo{xref, fsteps, st_d, st_i, out, info, rho, dbg}, b, f, tmem);
     __syncthreads();
   }
   cta::tmem_free(tmem);
@@ -457,7 +494,7 @@ struct qrw_mpc {
   int B, n_steps, N_gait, device, sms;
   MpcConst C;
   bool dbg_on = false;
-  int variant = 2;  // 2 = force-first CTA kernel (mpc_v2_kernel), 1 = v1 CTA kernel, 0 = warp per instance
+  int variant = 2;  // 2 = force-first CTA kernel with the twisted state chain (mpc_v2_kernel, default), 3 = nested-dissection state solve (mpc_v3_kernel, A/B), 1 = v1 CTA kernel, 0 = warp per instance
   double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr, *d_order = nullptr;
@@ -600,6 +637,7 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
+  CU(cudaFuncSetAttribute(mpc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nd::V3_SLAB_BYTES));
   *out = h;
   return 0;
 }
@@ -633,7 +671,19 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
-  if (h->variant == 2) {
+  if (h->variant == 3) {
+    int grid = 2 * h->sms;  // two CTAs (16 warps, 128 registers per thread) per SM
+    if (grid > h->B) grid = h->B;
+    const bool ord = h->use_order && h->B > grid;
+    if (ord) {
+      mpc_order_kernel<<<1, 1024, 0, s>>>(h->d_info, h->B, h->d_order);
+      ++g_launches;
+    }
+    mpc_v3_kernel<<<grid, nd::NT, nd::V3_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps, h->d_state,
+                                                          h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr,
+                                                          ord ? h->d_order : nullptr);
+  } else if (h->variant == 2) {
     int grid = 2 * h->sms;  // two CTAs (16 warps, 128 registers per thread) per SM
     if (grid > h->B) grid = h->B;
     const bool ord = h->use_order && h->B > grid;  // the order only matters when CTAs take more than one robot
@@ -669,15 +719,21 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
 // server needs when robots post their MPC requests at different times (qrw_b200/mpc_server.py).
 int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xref, const double* d_fsteps, void* stream) {
   if (!h || !d_k || !d_xref || !d_fsteps) return fail("qrw_mpc_run_indexed_device: null argument");
-  if (h->variant != 2) return fail("qrw_mpc_run_indexed_device: only the default kernel (variant 2) takes a per-robot index");
+  if (h->variant != 2 && h->variant != 3)
+    return fail("qrw_mpc_run_indexed_device: only the CTA kernels (variants 2 and 3) take a per-robot index");
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
   int grid = 2 * h->sms;
   if (grid > h->B) grid = h->B;
-  mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
-                                                        h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k,
-                                                        nullptr);
+  if (h->variant == 3)
+    mpc_v3_kernel<<<grid, nd::NT, nd::V3_SLAB_BYTES, s>>>(h->C, h->B, 0, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
+                                                          h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k,
+                                                          nullptr);
+  else
+    mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i,
+                                                          h->d_out, h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr,
+                                                          h->d_counter, d_k, nullptr);
   ++g_launches;
   CU(cudaGetLastError());
   return record_done(h->done, s);
@@ -768,8 +824,8 @@ int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
 }
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant) {
   if (!h) return fail("qrw_mpc_set_kernel: null handle");
-  if (variant < 0 || variant > 2)
-    return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance), 1 (CTA per instance, v1) or 2 (force-first CTA)");
+  if (variant < 0 || variant > 3)
+    return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance), 1 (CTA per instance, v1), 2 (force-first CTA, twisted state chain: default) or 3 (nested-dissection state solve)");
   h->variant = variant;
   return 0;
 }

@@ -184,6 +184,38 @@ __device__ __forceinline__ void tmem_st12(unsigned addr, const double* v) {
                "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23])
                : "memory");
 }
+// four doubles (8 columns): the tail of a 28-entry row segment
+struct TRow4 {
+  unsigned r[8];
+};
+__device__ __forceinline__ void tmem_ld4(unsigned addr, TRow4& t) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(t.r[0]), "=r"(t.r[1]), "=r"(t.r[2]), "=r"(t.r[3]), "=r"(t.r[4]), "=r"(t.r[5]), "=r"(t.r[6]), "=r"(t.r[7])
+               : "r"(addr));
+}
+__device__ __forceinline__ void tmem_get4(TRow4& t, double* v) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(t.r[0]), "+r"(t.r[1]), "+r"(t.r[2]), "+r"(t.r[3]), "+r"(t.r[4]), "+r"(t.r[5]), "+r"(t.r[6]), "+r"(t.r[7])
+               :
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __hiloint2double((int)t.r[2 * i + 1], (int)t.r[2 * i]);
+}
+__device__ __forceinline__ void tmem_st4(unsigned addr, const double* v) {
+  unsigned r[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) r[2 * i] = (unsigned)__double2loint(v[i]), r[2 * i + 1] = (unsigned)__double2hiint(v[i]);
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(addr), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+               "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+// v[0..3] = p[0..3] (16-byte aligned) as two LDS.128
+__device__ __forceinline__ void lds4(const double* p, double* v) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+#pragma unroll
+  for (int i = 0; i < 4; i += 2)
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[i]), "=d"(v[i + 1]) : "r"(a + 8 * i));
+}
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 }  // namespace cta
 }  // namespace qrw
@@ -224,6 +256,17 @@ inline void tmem_get12(TRow& t, double* v) {
   for (int i = 0; i < 12; ++i) v[i] = t.d[i];
 }
 void tmem_st12(unsigned addr, const double* v);
+struct TRow4 {
+  double d[4];
+};
+void tmem_ld4(unsigned addr, TRow4& t);
+inline void tmem_get4(TRow4& t, double* v) {
+  for (int i = 0; i < 4; ++i) v[i] = t.d[i];
+}
+void tmem_st4(unsigned addr, const double* v);
+inline void lds4(const double* p, double* v) {
+  for (int i = 0; i < 4; ++i) v[i] = p[i];
+}
 inline void tmem_wait_st() {}
 }  // namespace cta
 }  // namespace qrw

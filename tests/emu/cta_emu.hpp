@@ -215,10 +215,10 @@ inline double shfl_xor(double v, int m) {
 }
 // tensor memory: a thread reaches the lane (warp % 4) * 32 + lane of its quadrant and nothing else
 inline unsigned tmem_addr(unsigned base, int col) { return base + ((unsigned)(g_emu->cur & 96) << 16) + (unsigned)col; }
-inline double* tmem_row(unsigned addr) {
+inline double* tmem_row(unsigned addr, int ncol = 24) {
   Emu* e = g_emu;
   const int lane0 = (int)(addr >> 16), col = (int)(addr & 0xffff);
-  if (lane0 != (e->cur & 96) || (col & 1) || col + 24 > 256) {
+  if (lane0 != (e->cur & 96) || (col & 1) || col + ncol > 256) {
     fprintf(stderr, "cta_emu: bad TMEM access by thread %d (lane base %d, column %d)\n", e->cur, lane0, col);
     abort();
   }
@@ -231,6 +231,14 @@ inline void tmem_ld12(unsigned addr, TRow& t) {
 inline void tmem_st12(unsigned addr, const double* v) {
   double* p = tmem_row(addr);
   for (int i = 0; i < 12; ++i) p[i] = v[i];
+}
+inline void tmem_ld4(unsigned addr, TRow4& t) {
+  const double* p = tmem_row(addr, 8);
+  for (int i = 0; i < 4; ++i) t.d[i] = p[i];
+}
+inline void tmem_st4(unsigned addr, const double* v) {
+  double* p = tmem_row(addr, 8);
+  for (int i = 0; i < 4; ++i) p[i] = v[i];
 }
 inline int fetch_add(int* p, int v) {
   const int o = *p;
