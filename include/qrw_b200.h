@@ -142,6 +142,11 @@ int qrw_wbctick_destroy(qrw_wbctick_t* h);
 int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd,
                            const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
                            void* stream);
+/* same with f_cmd read with a stride (f_cmd + b * f_stride, f_stride >= 12): the MPC result + 12 with stride 24 * n_steps
+ * feeds x_f_mpc[12:24, 0] (Controller.py:258) without a gather */
+int qrw_wbctick_run_fstride_device(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, int f_stride,
+                                   const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                                   void* stream);
 int qrw_wbctick_run_host(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, const double* contacts,
                          const double* pgoals, const double* vgoals, const double* agoals);
 int qrw_wbctick_result_host(qrw_wbctick_t* h, double* tau_ff, double* qdes, double* vdes, double* f_res, double* ddq_cmd);
@@ -213,6 +218,39 @@ int qrw_planner_state_host(qrw_planner_t* h, double* past_gait, double* desired_
                            double* t_swing, int* flags);
 /* the `targetFootstep` argument of FootTrajectoryGenerator::update for callers that run stage 4 on its own: [B][12] */
 int qrw_planner_set_target_host(qrw_planner_t* h, const double* o_target);
+
+/* ---------------------------------------------------------------------------------------
+ * Closed control tick -- scripts/Controller.py:222-303 (Controller.compute) for B robots, entirely in HBM:
+ * planners -> MPC::run every k_mpc-th tick (MPC_Wrapper synchronous mode, scripts/MPC_Wrapper.py:64-71,122-148: the very
+ * first tick uses the default forces [0, 0, 8] per foot) -> whole-body tick with f_cmd = x_f_mpc[12:24, 0]
+ * (Controller.py:258,300), contacts = gait row 0 and the feet commands of :286-296.  What crosses PCIe per robot and
+ * tick: 156 B in (q.head(7), h_v, v_ref, joystick code), 288 B out (tau_ff, q_des, v_des).
+ * k_mpc = dt_mpc / dt_wbc, n_steps = T_mpc / dt_mpc (16 only, see qrw_mpc_create); q_init12 = wbc_controller.qdes[7:]
+ * before the first tick (Controller.py:153; host pointer to 12 doubles shared by the batch, NULL = the Solo12 stance
+ * of scripts/main_solo12_control.py).
+ * The tick index enters the kernels only through k % k_mpc and k != 0: qrw_tick_capture_period records the k_mpc ticks of
+ * one MPC period into a CUDA graph once, qrw_tick_replay_period / qrw_tick_period_host run one period per graph launch
+ * from per-period staging buffers (inputs [k_mpc][B][7 | 6 | 6], codes [k_mpc][B], outputs [k_mpc][B][12]).
+ * ------------------------------------------------------------------------------------- */
+typedef struct qrw_tick qrw_tick_t;
+int qrw_tick_create(qrw_tick_t** out, int batch, double dt_wbc, double dt_mpc, double T_gait, double T_mpc, int N_gait, double h_ref,
+                    const double* q_init12, int device);
+int qrw_tick_destroy(qrw_tick_t* h);
+/* one control tick k: q7 [B][7] (x y z, quaternion x y z w), h_v [B][6], v_ref [B][6], code [B] (NULL = 0) */
+int qrw_tick_run_device(qrw_tick_t* h, int k, const double* q7, const double* h_v, const double* v_ref, const int* code, void* stream);
+int qrw_tick_run_host(qrw_tick_t* h, int k, const double* q7, const double* h_v, const double* v_ref, const int* code);
+/* results of the latest tick, [B][12] each (any pointer may be NULL) */
+int qrw_tick_result_host(qrw_tick_t* h, double* tau_ff, double* q_des, double* v_des, double* f_res);
+int qrw_tick_result_device(qrw_tick_t* h, const double** tau_ff, const double** q_des, const double** v_des, const double** f_res);
+/* the planner / MPC / whole-body-tick objects the tick is composed of (getters, state snapshots); owned by the tick handle */
+int qrw_tick_parts(qrw_tick_t* h, qrw_planner_t** planner, qrw_mpc_t** mpc, qrw_wbctick_t** wbc);
+int qrw_tick_capture_period(qrw_tick_t* h);
+int qrw_tick_period_buffers(qrw_tick_t* h, double** q7, double** h_v, double** v_ref, int** code, const double** tau_ff,
+                            const double** q_des, const double** v_des);
+int qrw_tick_replay_period(qrw_tick_t* h, void* stream);
+/* one MPC period from host memory: H2D of [k_mpc][B][.] inputs, one graph launch, D2H of [k_mpc][B][12] outputs */
+int qrw_tick_period_host(qrw_tick_t* h, const double* q7, const double* h_v, const double* v_ref, const int* code, double* tau_ff,
+                         double* q_des, double* v_des);
 
 /* ---------------------------------------------------------------------------------------
  * MPC server -- the asynchronous mode of scripts/MPC_Wrapper.py (:47-52 shared Values / Arrays, :150-225 the child's

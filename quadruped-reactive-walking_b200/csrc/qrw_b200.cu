@@ -211,7 +211,8 @@ __global__ void __launch_bounds__(32 * WBC_WARPS) wbc_solve_kernel(const WbcCons
                                                                   const double* __restrict__ f_cmd,
                                                                   const double* __restrict__ RNEA, double* st,
                                                                   double* f_res, double* ddq_res, double* H,
-                                                                  int* info, int* counter, const int m_stride) {
+                                                                  int* info, int* counter, const int m_stride,
+                                                                  const int f_stride) {
   extern __shared__ __align__(16) double slab[];
   double* sl = slab + (threadIdx.x >> 5) * WBC_SLAB_DOUBLES;
   const int lane = threadIdx.x & 31;
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(32 * WBC_WARPS) wbc_solve_kernel(const WbcCons
     if (lane == 0) b = atomicAdd(counter, 1);
     b = __shfl_sync(0xffffffffu, b, 0);
     if (b >= B) break;
-    wbc_solve_instance(C, sl, M + (size_t)b * m_stride, Jc + (size_t)b * 216, f_cmd + (size_t)b * 12,
+    wbc_solve_instance(C, sl, M + (size_t)b * m_stride, Jc + (size_t)b * 216, f_cmd + (size_t)b * f_stride,
                        RNEA + (size_t)b * 6, st + (size_t)b * WBC_STATE_DOUBLES, first, f_res + (size_t)b * 12,
                        ddq_res + (size_t)b * 6, H ? H + (size_t)b * 144 : nullptr, info + 4 * b);
     __syncwarp();
@@ -508,6 +509,7 @@ struct qrw_wbc {
   WbcConst C;
   bool first = true;
   int m_stride = 324;  // 0: one M shared by the whole batch (the fused whole-body tick, where M is a model constant)
+  int f_stride = 12;   // doubles between the f_cmd blocks of consecutive robots (24 * n_steps when read from an MPC result)
   double *d_M = nullptr, *d_Jc = nullptr, *d_f = nullptr, *d_R = nullptr, *d_state = nullptr, *d_fres = nullptr,
          *d_ddq = nullptr, *d_H = nullptr;
   int *d_info = nullptr, *d_counter = nullptr;
@@ -935,7 +937,7 @@ int qrw_wbc_run_device(qrw_wbc_t* h, const double* d_M, const double* d_Jc, cons
   if (grid > need) grid = need;
   wbc_solve_kernel<<<grid, 32 * WBC_WARPS, WBC_WARPS * WBC_SLAB_BYTES, s>>>(
       h->C, h->B, h->first ? 1 : 0, d_M, d_Jc, d_f_cmd, d_RNEA, h->d_state, h->d_fres, h->d_ddq, h->d_H, h->d_info,
-      h->d_counter, h->m_stride);
+      h->d_counter, h->m_stride, h->f_stride);
   ++g_launches;
   CU(cudaGetLastError());
   h->first = false;  // QPWBC::initialized, src/QPWBC.cpp:23,254
@@ -1089,6 +1091,18 @@ int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, 
   CU(cudaGetLastError());
   return 0;
 }
+// Same tick with f_cmd read with a stride: f_cmd + b * f_stride (f_stride >= 12), e.g. the first-step contact forces
+// x_f_mpc[12:24, 0] straight out of an MPC result: qrw_mpc_result_device + 12 with stride 24 * n_steps.
+int qrw_wbctick_run_fstride_device(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, int f_stride,
+                                   const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                                   void* stream) {
+  if (!h) return fail("qrw_wbctick_run_fstride_device: null handle");
+  if (f_stride < 12) return fail("qrw_wbctick_run_fstride_device: f_stride < 12");
+  h->wbc->f_stride = f_stride;
+  const int rc = qrw_wbctick_run_device(h, q, dq, f_cmd, contacts, pgoals, vgoals, agoals, stream);
+  h->wbc->f_stride = 12;
+  return rc;
+}
 int qrw_wbctick_run_host(qrw_wbctick_t* h, const double* q, const double* dq, const double* f_cmd, const double* contacts,
                          const double* pgoals, const double* vgoals, const double* agoals) {
   if (!h || !q || !dq || !f_cmd || !contacts || !pgoals || !vgoals || !agoals)
@@ -1170,5 +1184,6 @@ int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, doubl
 
 }  // extern "C"
 #include "planner_abi.cuh"
+#include "tick_abi.cuh"
 #include <time.h>
 #include "transport_abi.cuh"

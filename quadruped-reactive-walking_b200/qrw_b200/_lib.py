@@ -83,6 +83,7 @@ _SIGNATURES = {
     "qrw_wbctick_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int]),
     "qrw_wbctick_destroy": (C.c_int, [_vp]),
     "qrw_wbctick_run_device": (C.c_int, [_vp] * 9),
+    "qrw_wbctick_run_fstride_device": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "qrw_wbctick_run_host": (C.c_int, [_vp] * 8),
     "qrw_wbctick_result_host": (C.c_int, [_vp] * 6),
     "qrw_wbctick_result_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 4),
@@ -101,6 +102,18 @@ _SIGNATURES = {
     "qrw_planner_outputs_host": (C.c_int, [_vp] * 11),
     "qrw_planner_state_host": (C.c_int, [_vp] * 7),
     "qrw_planner_set_target_host": (C.c_int, [_vp, _vp]),
+    "qrw_tick_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_double, _vp,
+                                  C.c_int]),
+    "qrw_tick_destroy": (C.c_int, [_vp]),
+    "qrw_tick_run_device": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "qrw_tick_run_host": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp]),
+    "qrw_tick_result_host": (C.c_int, [_vp] * 5),
+    "qrw_tick_result_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 4),
+    "qrw_tick_parts": (C.c_int, [_vp] + [C.POINTER(_vp)] * 3),
+    "qrw_tick_capture_period": (C.c_int, [_vp]),
+    "qrw_tick_period_buffers": (C.c_int, [_vp] + [C.POINTER(_vp)] * 7),
+    "qrw_tick_replay_period": (C.c_int, [_vp, _vp]),
+    "qrw_tick_period_host": (C.c_int, [_vp] * 8),
 }
 
 

@@ -289,6 +289,16 @@ class BatchedWbcTick:
             self.tau_ff, self.qdes, self.vdes, self.f_with_delta, self.ddq_cmd = outs
         return 0
 
+    def compute_from_mpc(self, q, dq, mpc_result, contacts, pgoals, vgoals, agoals, n_steps=N_STEPS):
+        """compute() with f_cmd = x_f_mpc[12:24, 0] read in place from an MPC result tensor [B, 24 n] (no gather): CUDA tensors."""
+        B = self.B
+        sizes = [19, 18, 4, 12, 12, 12]
+        args = [q, dq, contacts, pgoals, vgoals, agoals]
+        p = [_dev_ptr(a, B * s) for a, s in zip(args, sizes)]
+        f = C.c_void_p(mpc_result.data_ptr() + 12 * 8)
+        check(self._L.qrw_wbctick_run_fstride_device(self._h, p[0], p[1], f, 24 * int(n_steps), p[2], p[3], p[4], p[5], _torch_stream()))
+        return 0
+
     def result_tensors(self):
         """Zero-copy torch views (tau_ff, qdes, vdes, f_res), [B,12] each."""
         import torch
