@@ -26,14 +26,9 @@
 //
 // The same source compiles as a host-side warp emulation (see qrw_spmd.cuh) for CPU tests.
 #pragma once
-#include "qrw_spmd.cuh"
+#include "mpc_common.cuh"
 
 namespace qrw {
-
-constexpr int NS = 16;    // horizon steps (T_mpc / dt_mpc of src/config_solo12.yaml:11-13)
-constexpr int NX = 384;   // 24 * NS variables
-constexpr int NR = 704;   // 44 * NS constraint rows
-constexpr int NGMAX = 32; // max rows of the gait / fsteps matrices
 
 // shared slab layout (doubles)
 constexpr int OFF_SINV = 0;                 // 16 * 300 packed symmetric pivot-block inverses
@@ -50,30 +45,6 @@ constexpr int OFF_INT = OFF_WK + WK_SIZE;   // 128 ints
 constexpr int MPC_SLAB_DOUBLES = OFF_INT + 64;
 constexpr int MPC_SLAB_BYTES = MPC_SLAB_DOUBLES * 8;  // 75 264 B -> 3 warps per SM
 
-// per-instance persistent state in HBM (what OSQP's workspace + the MPC object carry between
-// calls: scaled iterates, rho, stale B_k values, gait and S_gait)
-constexpr int ST_X = 0, ST_Z = NX, ST_Y = NX + NR, ST_BANG = NX + 2 * NR, ST_RHO = ST_BANG + 576;
-constexpr int MPC_STATE_DOUBLES = 2376;  // 2369 rounded up to a multiple of 8
-constexpr int MPC_STATE_INTS = 64;       // gait bits [0,32) | S bits [32,48) | spare
-
-enum MpcStatus {  // OSQP status values
-  ST_SOLVED = 1,
-  ST_SOLVED_INACCURATE = 2,
-  ST_MAX_ITER = -2,
-  ST_NON_CVX = -7,
-  ST_UNSOLVED = -10
-};
-
-struct MpcConst {
-  double dt, dtm, mu, g8, sigma, alpha, eps_abs, eps_rel, rho0, adapt_tol;
-  double w[12];       // state weights            (MPC.cpp:330)
-  double wf;          // force weight 5e-5f       (MPC.cpp:346-348)
-  double gI[9];       // body inertia, row-major  (MPC.cpp:25-26)
-  double foot[12];    // default footholds 3 x 4  (MPC.cpp:24)
-  double off_com[3];  // (0, 0, -0.03)            (MPC.cpp:21)
-  int N_gait, max_iter, check_every, adapt_every;
-};
-
 struct MpcSlab {
   double *Sinv, *x, *z, *y, *D, *E, *bnd, *Bang, *wk;
   int* ib;
@@ -84,9 +55,6 @@ struct MpcSlab {
 };
 
 QRW_HD int sym_idx(int a, int b) { return a >= b ? (a * (a + 1)) / 2 + b : (b * (b + 1)) / 2 + a; }
-// global index of stage-local variable a of stage k: a<12 -> force f_k[a], else X_{k+1}[a-12]
-QRW_HD int gvar(int k, int a) { return a < 12 ? 192 + 12 * k + a : 12 * k + (a - 12); }
-
 // ------------------------------------------------------------------------------------------
 // Structured products with the UNSCALED constraint matrix A0 (pattern of ML, MPC.cpp:74-146).
 // Rows: [0,192) dynamics (k,i); [192,384) force-enable (k,j); [384,704) friction cone (k,foot,c).
@@ -175,15 +143,6 @@ QRW_HD int g_rows(int a, int rows[4]) {
   return 4;
 }
 
-struct RhoSet {
-  double rho, rho_eq, rinv, rinv_eq;
-  QRW_HD explicit RhoSet(double r) {
-    rho = dmin(dmax(r, 1e-6), 1e6);  // RHO_MIN / RHO_MAX
-    rho_eq = 1e3 * rho;              // RHO_EQ_OVER_RHO_INEQ
-    rinv = 1.0 / rho;
-    rinv_eq = 1.0 / rho_eq;
-  }
-};
 // rho of a constraint row: equality rows (u - l < RHO_TOL in scaled bounds) get 1e3 * rho.
 // Cone rows have l = -inf except every 5th, whose scaled width is 25 * E.
 QRW_HD bool row_is_eq(const MpcSlab& S, int r) {
@@ -873,41 +832,4 @@ QRW_HD void mpc_solve_instance(const MpcConst& C, double* slab, const double* xr
   QRW_SYNC();
 }
 
-}  // namespace qrw
-
-// ------------------------------------------------------------------------------------------
-// Host-side constants (the reference hard-codes them: MPC.cpp:17-29,330,346-348,527-539).
-// Float literals are widened exactly as the C++ does (e.g. 0.9f -> 0.8999999761581421).
-// ------------------------------------------------------------------------------------------
-namespace qrw {
-inline MpcConst make_mpc_const(double dt, int N_gait) {
-  MpcConst C;
-  const double mass = 2.50000279f;
-  C.dt = dt;
-  C.dtm = dt / mass;
-  C.mu = 0.9f;
-  C.g8 = -9.81f * dt;
-  C.sigma = 1e-6;
-  C.alpha = 1.6;
-  C.eps_abs = 1e-6;
-  C.eps_rel = 1e-6;
-  C.rho0 = 0.1;
-  C.adapt_tol = 5.0;
-  const double w[12] = {2.0f, 2.0f, 20.0f, 0.25f, 0.25f, 10.0f, 0.2f, 0.2f, 0.2f, 0.0f, 0.0f, 0.3f};
-  for (int i = 0; i < 12; ++i) C.w[i] = w[i];
-  C.wf = 5e-5f;
-  const double gi[9] = {3.09249e-2, -8.00101e-7, 1.865287e-5, -8.00101e-7, 5.106100e-2,
-                        1.245813e-4, 1.865287e-5, 1.245813e-4, 6.939757e-2};
-  for (int i = 0; i < 9; ++i) C.gI[i] = gi[i];
-  const double fh[12] = {0.19, 0.19, -0.19, -0.19, 0.15005, -0.15005, 0.15005, -0.15005, 0.0, 0.0, 0.0, 0.0};
-  for (int i = 0; i < 12; ++i) C.foot[i] = fh[i];
-  C.off_com[0] = 0.0;
-  C.off_com[1] = 0.0;
-  C.off_com[2] = -0.03;
-  C.N_gait = N_gait;
-  C.max_iter = 4000;
-  C.check_every = 25;
-  C.adapt_every = 200;
-  return C;
-}
 }  // namespace qrw

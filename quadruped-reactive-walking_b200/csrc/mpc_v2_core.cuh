@@ -33,7 +33,7 @@
 //     runs in that quadrant.  No tcgen05.mma anywhere: the tensor cores have no f64 kind, their memory is what is used.
 // It is still an exact solve of the same KKT system: the iterates differ from OSQP's by round-off only.
 #pragma once
-#include "mpc_core.cuh"
+#include "mpc_common.cuh"
 
 namespace qrw {
 namespace v2 {

@@ -30,7 +30,7 @@
 //     registers of their owner; everything else a stage owns in one shared-memory record; F_k (12x12) eliminated first,
 //     GF = E B0 D_f F^-1 and M = GF D_f B0' E formed at factorisation time.
 #pragma once
-#include "mpc_core.cuh"
+#include "mpc_common.cuh"
 
 namespace qrw {
 namespace nd {

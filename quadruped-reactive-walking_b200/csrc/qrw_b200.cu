@@ -8,7 +8,9 @@
 // Execution model of the MPC (mpc_v2_kernel): a persistent grid of 256-thread CTAs, two per SM (128 registers, 89 KB of
 // shared memory and 256 tensor-memory columns each), one robot per CTA at a time; CTAs pull robot indices from a global
 // work counter, so the large spread of ADMM iteration counts across a batch (25 ... 4000) does not leave SMs idle
-// behind a slow robot.  The two round-1 kernels (warp per robot, 24x24 block CTA) stay selectable for A/B parity runs.
+// behind a slow robot.  The shipped library contains this ONE MPC kernel; the two round-1 kernels (warp per robot, 24x24
+// block CTA) and the nested-dissection experiment (mpc_v3_core.cuh) are compiled only with -DQRW_AB_KERNELS into the A/B
+// test library (qrw_mpc_set_kernel selects among them there).
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -16,10 +18,12 @@
 #include <string>
 
 #include "../../include/qrw_b200.h"
+#include "mpc_v2_core.cuh"
+#ifdef QRW_AB_KERNELS  // A/B-test build only (tests/ab/libqrw_b200_ab.so): the round-1 kernels and the nested-dissection experiment
 #include "mpc_core.cuh"
 #include "mpc_cta_core.cuh"
-#include "mpc_v2_core.cuh"
 #include "mpc_v3_core.cuh"
+#endif
 #include "wbc_core.cuh"
 #include "solo12_core.cuh"
 
@@ -44,6 +48,7 @@ int fail(const std::string& what) {
 // ------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------
+#ifdef QRW_AB_KERNELS
 __global__ void __launch_bounds__(32) mpc_solve_kernel(const MpcConst C, const int B, const int first,
                                                        const double* __restrict__ xref,
                                                        const double* __restrict__ fsteps, double* st_d,
@@ -83,6 +88,8 @@ __global__ void __launch_bounds__(cta::NT, 2) mpc_cta_kernel(const MpcConst C, c
     __syncthreads();
   }
 }
+
+#endif  // QRW_AB_KERNELS
 
 // Force-first CTA-per-instance MPC solve (mpc_v2_core.cuh): persistent grid of 256-thread CTAs, two per SM
 // (128 registers per thread: at 80 the per-thread solver state spilled to local memory and the long-scoreboard
@@ -126,6 +133,7 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
   cta::tmem_free(tmem);
 }
 
+#ifdef QRW_AB_KERNELS
 // Nested-dissection CTA-per-instance MPC solve (mpc_v3_core.cuh, the default): persistent grid of 256-thread CTAs, two per
 // SM (128 registers per thread, 113 KB of shared memory and 256 tensor-memory columns each), pulling instance indices
 // from the global work counter.
@@ -161,6 +169,7 @@ __global__ void __launch_bounds__(nd::NT, 2) mpc_v3_kernel(const MpcConst C, con
   }
   cta::tmem_free(tmem);
 }
+#endif  // QRW_AB_KERNELS
 
 // Work order of the next launch: robots sorted by the ADMM iteration count of their previous solve, longest first
 // (counting sort, one CTA; iteration counts are multiples of check_every = 25 up to max_iter).  The persistent grid
@@ -304,21 +313,28 @@ __device__ __forceinline__ BaseState load_base(const double* q, const double* dq
   S.wb = s12::v3(dq[3], dq[4], dq[5]);
   return S;
 }
-__global__ void __launch_bounds__(128) wbc_tick_pre_kernel(const int B, const double* __restrict__ q,
-                                                           const double* __restrict__ dq,
-                                                           const double* __restrict__ contacts,
-                                                           const double* __restrict__ pgoals,
-                                                           const double* __restrict__ vgoals,
-                                                           const double* __restrict__ agoals, double* Jc,
-                                                           double* rnea6, double* ddq_cmd, double* vdes,
-                                                           double* qdes) {
+// One kernel for the whole tick (round 2; round 1 ran pre -> QPWBC -> post as three kernels with Jc / RNEA / ddq handed
+// over through HBM: 3.6 KB per robot on top of 1.24 KB algorithmic).  One WARP per robot, persistent grid pulling robot
+// indices from a counter:
+//   lanes 0..3 (one per leg)  leg kinematics, InvKin, contact-Jacobian rows and the chain's base wrench -> the warp's slab
+//   all lanes                 QPWBC (wbc_solve_instance) reading Jc / RNEA from the slab
+//   lanes 0..3                rnea(q, dq, ddq_cmd + [ddq_res; 0])[6:] - Jc[:, 6:]' f_res
+// The leg code is the register-hungry part (~250 registers when inlined); it is two real calls so that the QPWBC loop, which
+// every lane of the warp spends >90 % of the tick in, is allocated on its own and five 4-warp CTAs fit an SM.
+constexpr int WT_JC = WBC_SLAB_DOUBLES;        // [12 x 18] column-major contact Jacobian
+constexpr int WT_RNEA = WT_JC + 216;           // [6] base wrench of rnea(q, dq, [0; ddq_cmd]) (+ 2 pad)
+constexpr int WT_SLAB_DOUBLES = WT_RNEA + 8;
+constexpr int WT_SLAB_BYTES = WT_SLAB_DOUBLES * 8;
+#ifndef QRW_WT_CTAS
+#define QRW_WT_CTAS 4  // measured on B200, 65,536 robots: 3 CTAs/SM 2.37 ms, 4: 2.18 ms, 5 (96 registers: spills) 2.41 ms
+#endif
+constexpr int WT_WARPS = 4, WT_CTAS_PER_SM = QRW_WT_CTAS;
+
+__device__ __noinline__ void wbc_tick_pre_leg(const int leg, const double* __restrict__ qb, const double* __restrict__ dqb,
+                                              const double contact_flag, const double* __restrict__ pg,
+                                              const double* __restrict__ vgp, const double* __restrict__ agp, double* Jc_s,
+                                              double* rnea_s, double* ddq_out, double* vdes_out, double* qdes_out) {
   using namespace s12;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int leg = t & 3;
-  const bool valid = (t >> 2) < B;
-  const size_t b = valid ? (size_t)(t >> 2) : (size_t)(B - 1);
-  const double* qb = q + b * 19;
-  const double* dqb = dq + b * 18;
   double qj[3], dqj[3];
   for (int c = 0; c < 3; ++c) {
     qj[c] = qb[7 + 3 * leg + c];
@@ -330,13 +346,10 @@ __global__ void __launch_bounds__(128) wbc_tick_pre_kernel(const int B, const do
   V3 vf, wf, acl;
   foot_motion(K, dqj, vf, wf, acl);
   // InvKin::refreshAndCompute for this foot (Kp = 100, Kd = 20, src/InvKin.hpp:56-57)
-  const double* pg = pgoals + b * 12 + 3 * leg;
-  const double* vgp = vgoals + b * 12 + 3 * leg;
-  const double* agp = agoals + b * 12 + 3 * leg;
   const V3 e = v3(pg[0], pg[1], pg[2]) - K.pf;
   const V3 vg = v3(vgp[0], vgp[1], vgp[2]);
   V3 a = 100.0 * e - 20.0 * (vf - vg) + v3(agp[0], agp[1], agp[2]);
-  const bool contact = contacts[b * 4 + leg] != 0.0;
+  const bool contact = contact_flag != 0.0;
   if (contact) a = 0.0 * a;
   a = a - acl;  // af + wf x vf of InvKin.cpp:48 = classical acceleration of the foot point
   inv3(J, Ji);
@@ -350,29 +363,27 @@ __global__ void __launch_bounds__(128) wbc_tick_pre_kernel(const int B, const do
   const LegDyn D = leg_dynamics(leg, K, S.wb, v3(0.0, 0.0, 0.0), ab, dqj, ddq);
   double w6[6] = {D.f.x, D.f.y, D.f.z, D.n.x, D.n.y, D.n.z};
 #pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    w6[c] += __shfl_xor_sync(0xffffffffu, w6[c], 1);
-    w6[c] += __shfl_xor_sync(0xffffffffu, w6[c], 2);
+  for (int c = 0; c < 6; ++c) {  // the four leg lanes of the warp
+    w6[c] += __shfl_xor_sync(0xfu, w6[c], 1);
+    w6[c] += __shfl_xor_sync(0xfu, w6[c], 2);
   }
-  if (!valid) return;
   if (leg == 0) {
     V3 fb, nb;
     base_dynamics(S.wb, v3(0.0, 0.0, 0.0), ab, fb, nb);
-    double* r = rnea6 + b * 6;
-    r[0] = w6[0] + fb.x;
-    r[1] = w6[1] + fb.y;
-    r[2] = w6[2] + fb.z;
-    r[3] = w6[3] + nb.x;
-    r[4] = w6[4] + nb.y;
-    r[5] = w6[5] + nb.z;
+    rnea_s[0] = w6[0] + fb.x;
+    rnea_s[1] = w6[1] + fb.y;
+    rnea_s[2] = w6[2] + fb.z;
+    rnea_s[3] = w6[3] + nb.x;
+    rnea_s[4] = w6[4] + nb.y;
+    rnea_s[5] = w6[5] + nb.z;
   }
   for (int c = 0; c < 3; ++c) {
-    ddq_cmd[b * 12 + 3 * leg + c] = ddq[c];
-    vdes[b * 12 + 3 * leg + c] = c == 0 ? dv.x : (c == 1 ? dv.y : dv.z);
-    qdes[b * 12 + 3 * leg + c] = qj[c] + (c == 0 ? qs.x : (c == 1 ? qs.y : qs.z));
+    ddq_out[3 * leg + c] = ddq[c];
+    vdes_out[3 * leg + c] = c == 0 ? dv.x : (c == 1 ? dv.y : dv.z);
+    qdes_out[3 * leg + c] = qj[c] + (c == 0 ? qs.x : (c == 1 ? qs.y : qs.z));
   }
   // contact Jacobian rows of this foot (LOCAL_WORLD_ALIGNED, linear part): [R | R (e_c x pf) | R J_leg], zero if swinging
-  double* Jr = Jc + b * 216 + 3 * leg;
+  double* Jr = Jc_s + 3 * leg;
   const double on = contact ? 1.0 : 0.0;
   for (int c = 0; c < 18; ++c) {
     V3 col = v3(0.0, 0.0, 0.0);
@@ -388,35 +399,66 @@ __global__ void __launch_bounds__(128) wbc_tick_pre_kernel(const int B, const do
     Jr[12 * c + 2] = on * col.z;
   }
 }
-__global__ void __launch_bounds__(128) wbc_tick_post_kernel(const int B, const double* __restrict__ q,
-                                                            const double* __restrict__ dq,
-                                                            const double* __restrict__ contacts,
-                                                            const double* __restrict__ ddq_cmd,
-                                                            const double* __restrict__ ddq_res,
-                                                            const double* __restrict__ f_res, double* tau_ff) {
+__device__ __noinline__ void wbc_tick_post_leg(const int leg, const double* __restrict__ qb, const double* __restrict__ dqb,
+                                               const double contact_flag, const double* __restrict__ ddq_cmd,
+                                               const double* __restrict__ dr, const double* __restrict__ f_res, double* tau_ff) {
   using namespace s12;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int leg = t & 3;
-  if ((t >> 2) >= B) return;
-  const size_t b = (size_t)(t >> 2);
-  const double* qb = q + b * 19;
-  const double* dqb = dq + b * 18;
   double qj[3], dqj[3], ddq[3];
   for (int c = 0; c < 3; ++c) {
     qj[c] = qb[7 + 3 * leg + c];
     dqj[c] = dqb[6 + 3 * leg + c];
-    ddq[c] = ddq_cmd[b * 12 + 3 * leg + c];
+    ddq[c] = ddq_cmd[3 * leg + c];
   }
   const LegKin K = leg_kinematics(leg, qj);
   V3 J[3];
   leg_jacobian(K, J);
   const BaseState S = load_base(qb, dqb);
-  const double* dr = ddq_res + b * 6;
   const V3 ab = v3(dr[0], dr[1], dr[2]) + cross(S.wb, S.vb) + S12_GRAVITY * v3(S.R.c0.z, S.R.c1.z, S.R.c2.z);
   const LegDyn D = leg_dynamics(leg, K, S.wb, v3(dr[3], dr[4], dr[5]), ab, dqj, ddq);
-  const double* fr = f_res + b * 12 + 3 * leg;
-  const V3 fl = (contacts[b * 4 + leg] != 0.0) ? mulT(S.R, v3(fr[0], fr[1], fr[2])) : v3(0.0, 0.0, 0.0);  // R' f
-  for (int c = 0; c < 3; ++c) tau_ff[b * 12 + 3 * leg + c] = D.tau[c] - dot(J[c], fl);
+  const double* fr = f_res + 3 * leg;
+  const V3 fl = (contact_flag != 0.0) ? mulT(S.R, v3(fr[0], fr[1], fr[2])) : v3(0.0, 0.0, 0.0);  // R' f
+  for (int c = 0; c < 3; ++c) tau_ff[3 * leg + c] = D.tau[c] - dot(J[c], fl);
+}
+__global__ void __launch_bounds__(32 * WT_WARPS, WT_CTAS_PER_SM)
+    wbc_tick_kernel(const WbcConst C, const int B, const int first, const double* __restrict__ q, const double* __restrict__ dq,
+                    const double* __restrict__ f_cmd, const int f_stride, const double* __restrict__ contacts,
+                    const double* __restrict__ pgoals, const double* __restrict__ vgoals, const double* __restrict__ agoals,
+                    const double* __restrict__ M, const double* __restrict__ Yinv, double* st, double* f_res, double* ddq_res,
+                    int* info, double* ddq_cmd, double* vdes, double* qdes, double* tau_ff, double* Jc_dbg, double* rnea_dbg,
+                    int* counter) {
+  extern __shared__ __align__(16) double slab[];
+  double* sl = slab + (threadIdx.x >> 5) * WT_SLAB_DOUBLES;
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    int bi = 0;
+    if (lane == 0) bi = atomicAdd(counter, 1);
+    bi = __shfl_sync(0xffffffffu, bi, 0);
+    if (bi >= B) break;
+    const size_t b = (size_t)bi;
+    const double *qb = q + b * 19, *dqb = dq + b * 18;
+    if (lane < 4)
+      wbc_tick_pre_leg(lane, qb, dqb, contacts[b * 4 + lane], pgoals + b * 12 + 3 * lane, vgoals + b * 12 + 3 * lane,
+                       agoals + b * 12 + 3 * lane, sl + WT_JC, sl + WT_RNEA, ddq_cmd + b * 12, vdes + b * 12, qdes + b * 12);
+    __syncwarp();
+    if (Jc_dbg) {  // parity tests read the intermediates; the product path leaves them on chip
+      for (int e = lane; e < 216; e += 32) Jc_dbg[b * 216 + e] = sl[WT_JC + e];
+      if (lane < 6) rnea_dbg[b * 6 + lane] = sl[WT_RNEA + lane];
+    }
+    wbc_solve_instance(C, sl, M, sl + WT_JC, f_cmd + b * (size_t)f_stride, sl + WT_RNEA, st + b * WBC_STATE_DOUBLES, first,
+                       f_res + b * 12, ddq_res + b * 6, nullptr, info + 4 * b, Yinv);
+    __syncwarp();  // f_res / ddq_res / ddq_cmd written by other lanes of this warp are visible to the leg lanes
+    if (lane < 4)
+      wbc_tick_post_leg(lane, qb, dqb, contacts[b * 4 + lane], ddq_cmd + b * 12, ddq_res + b * 6, f_res + b * 12, tau_ff + b * 12);
+    __syncwarp();
+  }
+}
+// pinv(M[:6, :6]) of the batch-wide M, once per handle (same code as the per-robot path: bit-identical)
+__global__ void wbc_yinv_kernel(const double* __restrict__ M, double* Yinv) {
+  __shared__ double tmp[108];
+  if (threadIdx.x == 0) {
+    for (int e = 0; e < 36; ++e) tmp[72 + e] = M[(e % 6) + 18 * (e / 6)];
+    pinv6_serial(tmp + 72, Yinv, tmp, tmp + 36);
+  }
 }
 // the Pinocchio sub-boundary of scripts/solo12InvKin.py:47-59 on its own (parity tests, drop-in Solo12InvKin):
 // posf, vf, wf, af [B][4*3] column-major 4 x 3, Jf [B][12*12] column-major
@@ -495,7 +537,7 @@ struct qrw_mpc {
   int B, n_steps, N_gait, device, sms;
   MpcConst C;
   bool dbg_on = false;
-  int variant = 2;  // 2 = force-first CTA kernel with the twisted state chain (mpc_v2_kernel, default), 3 = nested-dissection state solve (mpc_v3_kernel, A/B), 1 = v1 CTA kernel, 0 = warp per instance
+  int variant = 2;  // 2 = mpc_v2_kernel (the one shipped); A/B build only: 3 = nested-dissection state solve, 1 = v1 CTA kernel, 0 = warp per instance
   double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr, *d_order = nullptr;
@@ -523,6 +565,8 @@ struct qrw_wbctick {
   double *d_q = nullptr, *d_dq = nullptr, *d_f = nullptr, *d_c = nullptr, *d_pg = nullptr, *d_vg = nullptr,
          *d_ag = nullptr;                                                      // staging of the host entry point
   double *d_Jc = nullptr, *d_rnea = nullptr, *d_ddq = nullptr, *d_vdes = nullptr, *d_qdes = nullptr, *d_tau = nullptr;
+  double* d_Yinv = nullptr;  // pinv(M[:6, :6]) of the batch-wide M
+  bool debug = false;        // copy Jc / RNEA out of the kernel (parity tests); off: they never leave the SM
 };
 
 // diag of crba(q = 0)[:6, :6] (scripts/QP_WBC.py:89-93): total mass, and the moments of inertia of the whole robot
@@ -636,10 +680,12 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CU(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)));
   CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CU(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming));
+  CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
+#ifdef QRW_AB_KERNELS
   CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
-  CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
   CU(cudaFuncSetAttribute(mpc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nd::V3_SLAB_BYTES));
+#endif
   *out = h;
   return 0;
 }
@@ -673,19 +719,29 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
+#ifdef QRW_AB_KERNELS
   if (h->variant == 3) {
-    int grid = 2 * h->sms;  // two CTAs (16 warps, 128 registers per thread) per SM
+    int grid = 2 * h->sms;
     if (grid > h->B) grid = h->B;
-    const bool ord = h->use_order && h->B > grid;
-    if (ord) {
-      mpc_order_kernel<<<1, 1024, 0, s>>>(h->d_info, h->B, h->d_order);
-      ++g_launches;
-    }
     mpc_v3_kernel<<<grid, nd::NT, nd::V3_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps, h->d_state,
                                                           h->d_state_i, h->d_out, h->d_info, h->d_rho,
-                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr,
-                                                          ord ? h->d_order : nullptr);
-  } else if (h->variant == 2) {
+                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr, nullptr);
+  } else if (h->variant == 1) {
+    int grid = 2 * h->sms;  // two 84 KB slabs (16 warps) per SM
+    if (grid > h->B) grid = h->B;
+    mpc_cta_kernel<<<grid, cta::NT, cta::CTA_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
+                                                              h->d_state, h->d_state_i, h->d_out, h->d_info,
+                                                              h->d_rho, h->dbg_on ? h->d_dbg : nullptr,
+                                                              h->d_counter);
+  } else if (h->variant == 0) {
+    int grid = 3 * h->sms;  // three 75 KB slabs per SM
+    if (grid > h->B) grid = h->B;
+    mpc_solve_kernel<<<grid, 32, MPC_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
+                                                      h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                      h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
+  } else
+#endif
+  {
     int grid = 2 * h->sms;  // two CTAs (16 warps, 128 registers per thread) per SM
     if (grid > h->B) grid = h->B;
     const bool ord = h->use_order && h->B > grid;  // the order only matters when CTAs take more than one robot
@@ -697,19 +753,6 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
                                                           h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
                                                           h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr,
                                                           ord ? h->d_order : nullptr);
-  } else if (h->variant == 1) {
-    int grid = 2 * h->sms;  // two 84 KB slabs (16 warps) per SM
-    if (grid > h->B) grid = h->B;
-    mpc_cta_kernel<<<grid, cta::NT, cta::CTA_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
-                                                              h->d_state, h->d_state_i, h->d_out, h->d_info,
-                                                              h->d_rho, h->dbg_on ? h->d_dbg : nullptr,
-                                                              h->d_counter);
-  } else {
-    int grid = 3 * h->sms;  // three 75 KB slabs per SM
-    if (grid > h->B) grid = h->B;
-    mpc_solve_kernel<<<grid, 32, MPC_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps,
-                                                      h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
-                                                      h->dbg_on ? h->d_dbg : nullptr, h->d_counter);
   }
   ++g_launches;
   CU(cudaGetLastError());
@@ -721,21 +764,15 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
 // server needs when robots post their MPC requests at different times (qrw_b200/mpc_server.py).
 int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xref, const double* d_fsteps, void* stream) {
   if (!h || !d_k || !d_xref || !d_fsteps) return fail("qrw_mpc_run_indexed_device: null argument");
-  if (h->variant != 2 && h->variant != 3)
-    return fail("qrw_mpc_run_indexed_device: only the CTA kernels (variants 2 and 3) take a per-robot index");
+  if (h->variant != 2) return fail("qrw_mpc_run_indexed_device: only the default kernel (variant 2) takes a per-robot index");
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
   int grid = 2 * h->sms;
   if (grid > h->B) grid = h->B;
-  if (h->variant == 3)
-    mpc_v3_kernel<<<grid, nd::NT, nd::V3_SLAB_BYTES, s>>>(h->C, h->B, 0, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
-                                                          h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k,
-                                                          nullptr);
-  else
-    mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i,
-                                                          h->d_out, h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr,
-                                                          h->d_counter, d_k, nullptr);
+  mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
+                                                        h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k,
+                                                        nullptr);
   ++g_launches;
   CU(cudaGetLastError());
   return record_done(h->done, s);
@@ -826,8 +863,14 @@ int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
 }
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant) {
   if (!h) return fail("qrw_mpc_set_kernel: null handle");
+#ifdef QRW_AB_KERNELS
   if (variant < 0 || variant > 3)
     return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance), 1 (CTA per instance, v1), 2 (force-first CTA, twisted state chain: default) or 3 (nested-dissection state solve)");
+#else
+  if (variant != 2)
+    return fail("qrw_mpc_set_kernel: this library contains the one MPC kernel it ships (variant 2); variants 0, 1 and 3 exist only in the A/B "
+                "test build (-DQRW_AB_KERNELS, tests/ab/libqrw_b200_ab.so)");
+#endif
   h->variant = variant;
   return 0;
 }
@@ -1060,7 +1103,19 @@ int qrw_wbctick_create(qrw_wbctick_t** out, int batch, int device) {
     CU(cudaMalloc(p[i], B * sz[i] * sizeof(double)));
     CU(cudaMemset(*p[i], 0, B * sz[i] * sizeof(double)));
   }
+  CU(cudaMalloc(&h->d_Yinv, 36 * sizeof(double)));
+  wbc_yinv_kernel<<<1, 32>>>(w->d_M, h->d_Yinv);
+  ++g_launches;
+  CU(cudaGetLastError());
+  CU(cudaFuncSetAttribute(wbc_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WT_WARPS * WT_SLAB_BYTES));
+  CU(cudaDeviceSynchronize());
   *out = h;
+  return 0;
+}
+// 1: every tick also copies the intermediates handed to QPWBC (Jc, RNEA) to HBM for qrw_wbctick_debug_host; 0 (default): off
+int qrw_wbctick_set_debug(qrw_wbctick_t* h, int on) {
+  if (!h) return fail("qrw_wbctick_set_debug: null handle");
+  h->debug = on != 0;
   return 0;
 }
 int qrw_wbctick_destroy(qrw_wbctick_t* h) {
@@ -1069,6 +1124,7 @@ int qrw_wbctick_destroy(qrw_wbctick_t* h) {
   double* p[13] = {h->d_q, h->d_dq, h->d_f, h->d_c, h->d_pg, h->d_vg, h->d_ag, h->d_Jc, h->d_rnea, h->d_ddq, h->d_vdes,
                    h->d_qdes, h->d_tau};
   for (double* x : p) cudaFree(x);
+  cudaFree(h->d_Yinv);
   qrw_wbc_destroy(h->wbc);
   delete h;
   return 0;
@@ -1080,15 +1136,18 @@ int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, 
     return fail("qrw_wbctick_run_device: null argument");
   CU(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
-  const unsigned grid = (unsigned)((4LL * h->B + 127) / 128);
-  wbc_tick_pre_kernel<<<grid, 128, 0, s>>>(h->B, q, dq, contacts, pgoals, vgoals, agoals, h->d_Jc, h->d_rnea, h->d_ddq,
-                                           h->d_vdes, h->d_qdes);
+  qrw_wbc* w = h->wbc;
+  CU(cudaMemsetAsync(w->d_counter, 0, sizeof(int), s));
+  int grid = WT_CTAS_PER_SM * w->sms;  // persistent: 5 CTAs x 4 warps x 9.7 KB per SM
+  const int need = (h->B + WT_WARPS - 1) / WT_WARPS;
+  if (grid > need) grid = need;
+  wbc_tick_kernel<<<grid, 32 * WT_WARPS, WT_WARPS * WT_SLAB_BYTES, s>>>(
+      w->C, h->B, w->first ? 1 : 0, q, dq, f_cmd, w->f_stride, contacts, pgoals, vgoals, agoals, w->d_M, h->d_Yinv, w->d_state,
+      w->d_fres, w->d_ddq, w->d_info, h->d_ddq, h->d_vdes, h->d_qdes, h->d_tau, h->debug ? h->d_Jc : nullptr,
+      h->debug ? h->d_rnea : nullptr, w->d_counter);
   ++g_launches;
   CU(cudaGetLastError());
-  if (qrw_wbc_run_device(h->wbc, h->wbc->d_M, h->d_Jc, f_cmd, h->d_rnea, s)) return 1;
-  wbc_tick_post_kernel<<<grid, 128, 0, s>>>(h->B, q, dq, contacts, h->d_ddq, h->wbc->d_ddq, h->wbc->d_fres, h->d_tau);
-  ++g_launches;
-  CU(cudaGetLastError());
+  w->first = false;  // QPWBC::initialized, src/QPWBC.cpp:23,254
   return 0;
 }
 // Same tick with f_cmd read with a stride: f_cmd + b * f_stride (f_stride >= 12), e.g. the first-step contact forces

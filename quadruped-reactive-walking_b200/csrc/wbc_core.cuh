@@ -206,9 +206,11 @@ QRW_HD void wbc_factor(const WbcConst& C, double* sl, double rho, double cscale)
 
 // One QPWBC::run.  M 18x18, Jc 12x18 column-major.  st: persistent state.  Outputs f_res[12],
 // ddq_res[6], optional H[144] (column-major), info {iters, status, n_factor}.
+// Yinv_pre (optional): pinv(M[:6, :6]) computed beforehand by the same pinv6_serial -- the whole-body tick passes one M for
+// the whole batch (crba at the zero configuration is a model constant), so its pseudo-inverse is computed once per handle.
 QRW_HD void wbc_solve_instance(const WbcConst& C, double* sl, const double* M, const double* Jc,
                                const double* f_cmd, const double* RNEA, double* st, int first,
-                               double* f_res, double* ddq_res, double* H_out, int* info) {
+                               double* f_res, double* ddq_res, double* H_out, int* info, const double* Yinv_pre = nullptr) {
   double *A = sl + W_A, *gam = sl + W_GAM, *H = sl + W_H, *g = sl + W_G, *D = sl + W_D, *E = sl + W_E,
          *Kinv = sl + W_KINV, *x = sl + W_X, *z = sl + W_Z, *y = sl + W_Y, *xt = sl + W_XT,
          *rhs = sl + W_RHS, *lo = sl + W_L, *up = sl + W_U, *qh = sl + W_Q, *ev = sl + W_EV,
@@ -223,8 +225,14 @@ QRW_HD void wbc_solve_instance(const WbcConst& C, double* sl, const double* M, c
     }
   }
   QRW_SYNC();
-  QRW_LANES(l) {
-    if (l == 0) pinv6_serial(tmp + 72, Yinv, tmp, tmp + 36);
+  if (Yinv_pre) {
+    QRW_LANES(l) {
+      for (int e = l; e < 36; e += 32) Yinv[e] = Yinv_pre[e];
+    }
+  } else {
+    QRW_LANES(l) {
+      if (l == 0) pinv6_serial(tmp + 72, Yinv, tmp, tmp + 36);
+    }
   }
   QRW_SYNC();
   double* Xf = tmp;  // X f_cmd - RNEA (6)

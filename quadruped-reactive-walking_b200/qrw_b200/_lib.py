@@ -38,6 +38,22 @@ def build_library(force=False, verbose=False):
     return _SO
 
 
+_AB_SO = os.path.join(os.path.dirname(_ROOT), "tests", "ab", "libqrw_b200_ab.so")
+
+
+def build_ab_library(force=False):
+    """TEST INFRASTRUCTURE: the same source with -DQRW_AB_KERNELS -- the superseded MPC kernels (warp per robot, 24x24 block
+    CTA) and the nested-dissection experiment next to the shipped one, selectable with qrw_mpc_set_kernel.  Only the A/B
+    parity tests load it (tests/ab/); the product library contains one MPC kernel."""
+    srcs = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)]
+    if not force and os.path.exists(_AB_SO) and all(os.path.getmtime(x) <= os.path.getmtime(_AB_SO) for x in srcs):
+        return _AB_SO
+    os.makedirs(os.path.dirname(_AB_SO), exist_ok=True)
+    nvcc = os.environ.get("NVCC", "nvcc")
+    subprocess.check_call([nvcc] + NVCC_FLAGS + ["-DQRW_AB_KERNELS", "-o", _AB_SO, os.path.join(_CSRC, "qrw_b200.cu")])
+    return _AB_SO
+
+
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
 _vp = C.c_void_p
@@ -88,6 +104,7 @@ _SIGNATURES = {
     "qrw_wbctick_result_host": (C.c_int, [_vp] * 6),
     "qrw_wbctick_result_device": (C.c_int, [_vp] + [C.POINTER(_vp)] * 4),
     "qrw_wbctick_debug_host": (C.c_int, [_vp] * 4),
+    "qrw_wbctick_set_debug": (C.c_int, [_vp, C.c_int]),
     "qrw_wbctick_set_desired_host": (C.c_int, [_vp, _vp, _vp]),
     "qrw_wbctick_run_ctrl_device": (C.c_int, [_vp, C.c_double, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "qrw_solo12_base_inertia": (C.c_int, [_vp]),
@@ -122,20 +139,34 @@ def exported_symbols():
     return sorted(_SIGNATURES)
 
 
-def load_library():
-    """Load libqrw_b200.so; raises QrwError (never falls back) if it has not been built."""
+def _bind(path):
+    L = C.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    return L
+
+
+_others = {}
+
+
+def load_library(path=None):
+    """Load libqrw_b200.so; raises QrwError (never falls back) if it has not been built.  `path` loads another build of the
+    same ABI next to it (the A/B test library) without replacing the default."""
     global _lib
+    if path is not None:
+        if path not in _others:
+            if not os.path.exists(path):
+                raise QrwError(f"{path} not found")
+            _others[path] = _bind(path)
+        return _others[path]
     if _lib is None:
         if not os.path.exists(_SO):
             raise QrwError(
                 f"{_SO} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()'). "
                 "qrw_b200 has no CPU fallback.")
-        L = C.CDLL(_SO)
-        for name, (res, args) in _SIGNATURES.items():
-            f = getattr(L, name)
-            f.restype = res
-            f.argtypes = args
-        _lib = L
+        _lib = _bind(_SO)
     return _lib
 
 

@@ -66,8 +66,8 @@ class BatchedMPC:
     names (python/gepadd.cpp:22-31); xref is [B, 12*(n+1)], fsteps [B, N_gait*12], result [B, 24*n].
     """
 
-    def __init__(self, batch, dt=0.02, n_steps=N_STEPS, T_gait=0.32, N_gait=20, device=0):
-        self._L = load_library()
+    def __init__(self, batch, dt=0.02, n_steps=N_STEPS, T_gait=0.32, N_gait=20, device=0, library=None):
+        self._L = load_library(library)  # `library`: another build of the same ABI (the A/B test library)
         self.B, self.n, self.N_gait, self.device = int(batch), int(n_steps), int(N_gait), int(device)
         h = C.c_void_p()
         check(self._L.qrw_mpc_create(C.byref(h), self.B, float(dt), self.n, float(T_gait), self.N_gait, self.device))
@@ -129,7 +129,8 @@ class BatchedMPC:
         check(self._L.qrw_mpc_set_max_iter(self._h, int(k)))
 
     def set_kernel(self, variant):
-        """2 = force-first CTA kernel with tensor-memory rows (default), 1 = v1 CTA kernel, 0 = warp per instance (v0)."""
+        """2 = the shipped kernel (force-first elimination, twisted state chain, tensor-memory rows).  The A/B test library
+        (tests/ab, -DQRW_AB_KERNELS) also has 3 = nested-dissection state solve, 1 = v1 CTA kernel, 0 = warp per robot."""
         check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
 
     def set_work_order(self, longest_first):
@@ -255,16 +256,20 @@ class BatchedInvKin:
 
 class BatchedWbcTick:
     """B robots' ``wbc_controller.compute`` (reference scripts/QP_WBC.py:52-131): Solo12 kinematics / RNEA, InvKin,
-    QPWBC and the feed-forward torque in three kernels.  compute(q, dq, f_cmd, contacts, pgoals, vgoals, agoals) with
+    QPWBC and the feed-forward torque in ONE kernel (a warp per robot; Jc / RNEA never leave the SM).  compute(q, dq, f_cmd, contacts, pgoals, vgoals, agoals) with
     q [B,19], dq [B,18], f_cmd [B,12], contacts [B,4], goals [B,12] (3x4 column-major); results in tau_ff, qdes, vdes,
     f_with_delta, ddq_cmd ([B,12] each)."""
 
-    def __init__(self, batch, device=0):
+    kernels_per_tick = 1
+
+    def __init__(self, batch, device=0, debug=False):
         self._L = load_library()
         self.B, self.device = int(batch), int(device)
         h = C.c_void_p()
         check(self._L.qrw_wbctick_create(C.byref(h), self.B, self.device))
         self._h = h
+        if debug:  # debug(): also copy the intermediates handed to QPWBC (Jc, RNEA) to HBM every tick
+            check(self._L.qrw_wbctick_set_debug(self._h, 1))
         self.tau_ff = self.qdes = self.vdes = self.f_with_delta = self.ddq_cmd = None
 
     def close(self):

@@ -62,6 +62,15 @@ def emu():
     return C.CDLL(os.path.join(d, "libqrw_emu.so"))
 
 
+@pytest.fixture(scope="session")
+def ab_library():
+    """Path of the A/B build of the library (tests/ab/libqrw_b200_ab.so: -DQRW_AB_KERNELS adds the superseded MPC kernels and
+    the nested-dissection experiment).  Test infrastructure; built by __graft_entry__.build() so that it travels to the GPU box."""
+    from qrw_b200 import _lib
+
+    return _lib.build_ab_library()
+
+
 def assert_forces_close(got, want, what=""):
     import numpy as np
 

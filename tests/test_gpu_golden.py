@@ -11,14 +11,12 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(ROOT, "tests", "golden")
 
 
-@pytest.mark.parametrize("kernel", [2, 1])
 @pytest.mark.parametrize("name,B", [("mpc_config1_single_trot", 1), ("mpc_trot_b8", 8), ("mpc_mixed_b10", 10)])
-def test_mpc_golden(name, B, kernel):
+def test_mpc_golden(name, B):
     from qrw_b200 import BatchedMPC
 
     g = np.load(os.path.join(GOLD, name + ".npz"))
     m = BatchedMPC(B)
-    m.set_kernel(kernel)
     for t in range(int(g["ticks"])):
         m.run(t, g[f"xref{t}"], g[f"fsteps{t}"])
         assert np.array_equal(m.get_gait(), g[f"gait{t}"]) and np.array_equal(m.get_Sgait(), g[f"sgait{t}"])

@@ -8,11 +8,11 @@ from conftest import assert_forces_close
 pytestmark = pytest.mark.gpu
 
 
-def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=2):
+def _closed_loop(oracle, gaits, B, seed, ticks, threads=8, kernel=2, library=None):
     from qrw_b200 import BatchedMPC, workloads as wl
 
     w = wl.MpcWorkload(B, seed, gaits=gaits, ticks=ticks + 1)
-    gpu, cpu = BatchedMPC(B), oracle.OracleMPC(B)
+    gpu, cpu = BatchedMPC(B, library=library), oracle.OracleMPC(B)
     gpu.set_kernel(kernel)
     x0 = None
     for t in range(ticks):
@@ -52,25 +52,41 @@ def test_config1_single_trot(oracle):
     assert np.abs(f[0, 3:9]).max() < 1e-4
 
 
-@pytest.mark.parametrize("kernel", [2, 1, 0])
-def test_trot_batch_closed_loop(oracle, kernel):
-    _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4, kernel=kernel)
+def test_trot_batch_closed_loop(oracle):
+    _closed_loop(oracle, ("trot",), B=64, seed=1, ticks=4)
 
 
-@pytest.mark.parametrize("kernel", [2, 1, 0])
-def test_mixed_gaits_closed_loop(oracle, kernel):
-    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3, kernel=kernel)
+def test_mixed_gaits_closed_loop(oracle):
+    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3)
 
 
-@pytest.mark.parametrize("va,vb", [(2, 1), (1, 0)])
-def test_kernel_variants_agree_at_full_size(va, vb):
-    """4096 trot instances, cold tick + one update tick: the kernel variants (2 = force-first CTA, 1 = v1 CTA,
+def test_the_shipped_library_has_one_mpc_kernel():
+    from qrw_b200 import BatchedMPC
+    from qrw_b200._lib import QrwError
+
+    m = BatchedMPC(1)
+    m.set_kernel(2)
+    for v in (0, 1, 3):
+        with pytest.raises(QrwError, match="A/B"):
+            m.set_kernel(v)
+
+
+# ---- A/B build (tests/ab/libqrw_b200_ab.so, -DQRW_AB_KERNELS): the superseded kernels and the nested-dissection experiment
+@pytest.mark.parametrize("kernel", [3, 1, 0])
+def test_ab_kernels_closed_loop(oracle, ab_library, kernel):
+    _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3, kernel=kernel, library=ab_library)
+
+
+@pytest.mark.parametrize("va,vb", [(2, 3), (2, 1), (1, 0)])
+def test_kernel_variants_agree_at_full_size(ab_library, va, vb):
+    """4096 trot instances, cold tick + one update tick: the kernel variants (2 = shipped, 3 = nested dissection, 1 = v1 CTA,
     0 = warp per instance) follow the same iterate sequence (same iteration counts, results equal to round-off)."""
     from qrw_b200 import BatchedMPC, workloads as wl
 
     B = 4096
     w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=3)
-    a, b = BatchedMPC(B), BatchedMPC(B)
+    a = BatchedMPC(B) if va == 2 else BatchedMPC(B, library=ab_library)  # variant 2 = the SHIPPED library's kernel
+    b = BatchedMPC(B, library=ab_library)
     a.set_kernel(va)
     b.set_kernel(vb)
     x0 = None

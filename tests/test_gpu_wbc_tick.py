@@ -30,7 +30,7 @@ def test_wbc_tick_matches_oracle(oracle, level):
     from qrw_b200 import BatchedWbcTick, workloads as wl
 
     B = 300
-    gpu, cpu = BatchedWbcTick(B), oracle.OracleWBC(B)
+    gpu, cpu = BatchedWbcTick(B, debug=True), oracle.OracleWBC(B)
     for call in range(3):  # the QP warm start carries over
         args = wl.wbc_tick_inputs(B, seed=40 + call, level_base=level)
         gpu.compute(*args)
