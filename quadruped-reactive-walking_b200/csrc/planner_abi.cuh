@@ -119,16 +119,16 @@ int qrw_planner_create(qrw_planner_t** out, int batch, double dt_mpc, double dt_
   for (int i = 0; i < 12; ++i) C.shoulders[i] = h->ftg_target[i] = h->ftg_pos[i] = sh[i];
   const size_t B = (size_t)batch;
   h->M.B = batch;
-  CU(cudaMalloc(&h->M.st, B * qrw::plan::PLAN_STATE_DOUBLES * sizeof(double)));
-  CU(cudaMalloc(&h->M.bits, B * 6 * sizeof(unsigned long long)));
-  CU(cudaMalloc(&h->M.flags, B * sizeof(int)));
-  CU(cudaMalloc(&h->M.xref, B * 12 * (n_steps + 1) * sizeof(double)));
-  CU(cudaMalloc(&h->M.fsteps, B * 12 * N_gait * sizeof(double)));
-  CU(cudaMalloc(&h->d_q, B * 7 * sizeof(double)));
-  CU(cudaMalloc(&h->d_v, B * 6 * sizeof(double)));
-  CU(cudaMalloc(&h->d_vref, B * 6 * sizeof(double)));
-  CU(cudaMalloc(&h->d_code, B * sizeof(int)));
-  CU(cudaStreamCreate(&h->stream));
+  CUH(cudaMalloc(&h->M.st, B * qrw::plan::PLAN_STATE_DOUBLES * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->M.bits, B * 6 * sizeof(unsigned long long)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->M.flags, B * sizeof(int)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->M.xref, B * 12 * (n_steps + 1) * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->M.fsteps, B * 12 * N_gait * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->d_q, B * 7 * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->d_v, B * 6 * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->d_vref, B * 6 * sizeof(double)), qrw_planner_destroy(h));
+  CUH(cudaMalloc(&h->d_code, B * sizeof(int)), qrw_planner_destroy(h));
+  CUH(cudaStreamCreate(&h->stream), qrw_planner_destroy(h));
   if (planner_reset(h)) return 1;
   *out = h;
   return 0;

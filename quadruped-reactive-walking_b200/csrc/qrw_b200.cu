@@ -13,6 +13,7 @@
 // test library (qrw_mpc_set_kernel selects among them there).
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -23,6 +24,7 @@
 #include "mpc_core.cuh"
 #include "mpc_cta_core.cuh"
 #include "mpc_v3_core.cuh"
+#include "mpc_v4_core.cuh"
 #endif
 #include "wbc_core.cuh"
 #include "solo12_core.cuh"
@@ -32,7 +34,7 @@ using namespace qrw;
 namespace {
 
 thread_local std::string g_err;
-long long g_launches = 0;
+std::atomic<long long> g_launches{0};  // incremented from any calling thread
 
 int fail(const std::string& what) {
   g_err = what;
@@ -43,6 +45,17 @@ int fail(const std::string& what) {
     cudaError_t e_ = (call);                                                              \
     if (e_ != cudaSuccess)                                                                \
       return fail(std::string(#call) + ": " + cudaGetErrorString(e_));                    \
+  } while (0)
+// inside a *_create after the handle exists: a failed allocation releases everything allocated so far (the destroy functions
+// tolerate null members) instead of leaking the handle and its device / pinned memory
+#define CUH(call, destroy)                                                                \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      fail(std::string(#call) + ": " + cudaGetErrorString(e_));                           \
+      destroy;                                                                            \
+      return 1;                                                                           \
+    }                                                                                     \
   } while (0)
 
 // ------------------------------------------------------------------------------------------
@@ -132,6 +145,51 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
   }
   cta::tmem_free(tmem);
 }
+
+#ifdef QRW_AB_KERNELS
+// Super-stage chain variant (mpc_v4_core.cuh): same launch shape as mpc_v2_kernel; four chain warps instead of three
+// Force-first CTA-per-instance MPC solve (mpc_v4_core.cuh): persistent grid of 256-thread CTAs, two per SM
+// (128 registers per thread: at 80 the per-thread solver state spilled to local memory and the long-scoreboard
+// stalls of those reloads dominated, profiles/r01_ncu_mpc_v2*.txt), pulling instance indices from the global
+// work counter.  The
+// warp that runs the sequential state recurrences differs between the CTAs that share an SM, so that they
+// do not pile up on one SM sub-partition.
+__global__ void __launch_bounds__(v4::NT, 2) mpc_v4_kernel(const MpcConst C, const int B, const int first,
+                                                           const int sms, const double* __restrict__ xref,
+                                                           const double* __restrict__ fsteps, double* st_d,
+                                                           int* st_i, double* out, int* info, double* rho,
+                                                           double* dbg, int* counter, const int* __restrict__ k_arr,
+                                                           const int* __restrict__ order) {
+  extern __shared__ __align__(16) double slab[];
+  int* next = reinterpret_cast<int*>(slab + v4::V_INT) + 127;
+  const int recw = (blockIdx.x / sms) & 3;
+  // 256 of the SM's 512 tensor-memory columns for the whole life of this (persistent) CTA: the matrix rows of the solve
+  const unsigned tmem = cta::tmem_alloc(reinterpret_cast<unsigned*>(slab + v4::V_INT) + v4::V4_TMEM_SLOT);
+  for (;;) {
+    if (threadIdx.x == 0) {
+      const int idx = atomicAdd(counter, 1);
+      *next = idx < B ? (order ? order[idx] : idx) : B;  // longest-expected solves first (mpc_order_kernel)
+    }
+    __syncthreads();
+    const int b = *next;
+    if (b >= B) break;
+    int f = first;
+    if (k_arr) {  // per-instance call index (qrw_mpc_run_indexed_device): < 0 = no call for this robot in this launch
+      const int kb = k_arr[b];
+      if (kb < 0) {
+        __syncthreads();
+        continue;
+      }
+      f = kb == 0 ? 1 : 0;
+    }
+    v4::mpc_v4_solve(C, slab, xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * C.N_gait,
+                     st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, f,
+                     out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw, tmem);
+    __syncthreads();
+  }
+  cta::tmem_free(tmem);
+}
+#endif  // QRW_AB_KERNELS
 
 #ifdef QRW_AB_KERNELS
 // Nested-dissection CTA-per-instance MPC solve (mpc_v3_core.cuh, the default): persistent grid of 256-thread CTAs, two per
@@ -597,7 +655,7 @@ static void solo12_base_inertia(double Y[6]) {
 extern "C" {
 
 const char* qrw_last_error(void) { return g_err.c_str(); }
-long long qrw_launch_count(void) { return g_launches; }
+long long qrw_launch_count(void) { return g_launches.load(); }
 int qrw_device_sm_count(int device, int* sm_count) {
   int n = sm_count_of(device);
   if (n <= 0) return fail("no usable CUDA device (this library has no CPU fallback)");
@@ -659,32 +717,33 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   h->sms = sm_count_of(device);
   h->C = make_mpc_const(dt, N_gait);
   const size_t B = (size_t)batch;
-  CU(cudaMalloc(&h->d_xref, B * 12 * (NS + 1) * sizeof(double)));
-  CU(cudaMalloc(&h->d_fsteps, B * 12 * N_gait * sizeof(double)));
-  CU(cudaMalloc(&h->d_out, B * 24 * NS * sizeof(double)));
-  CU(cudaMalloc(&h->d_state, B * MPC_STATE_DOUBLES * sizeof(double)));
-  CU(cudaMalloc(&h->d_state_i, B * MPC_STATE_INTS * sizeof(int)));
-  CU(cudaMalloc(&h->d_rho, B * sizeof(double)));
-  CU(cudaMalloc(&h->d_info, B * 4 * sizeof(int)));
-  CU(cudaMalloc(&h->d_counter, sizeof(int)));
-  CU(cudaMalloc(&h->d_order, B * sizeof(int)));
-  CU(cudaMalloc(&h->d_gait, B * 4 * N_gait * sizeof(double)));
-  CU(cudaMalloc(&h->d_sgait, B * 12 * NS * sizeof(double)));
-  CU(cudaMemset(h->d_state, 0, B * MPC_STATE_DOUBLES * sizeof(double)));
-  CU(cudaMemset(h->d_state_i, 0, B * MPC_STATE_INTS * sizeof(int)));
-  CU(cudaMemset(h->d_out, 0, B * 24 * NS * sizeof(double)));
-  CU(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)));
-  CU(cudaMemset(h->d_rho, 0, B * sizeof(double)));
-  CU(cudaMallocHost(&h->h_xref, B * 12 * (NS + 1) * sizeof(double)));
-  CU(cudaMallocHost(&h->h_fsteps, B * 12 * N_gait * sizeof(double)));
-  CU(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)));
-  CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  CU(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming));
-  CU(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES));
+  CUH(cudaMalloc(&h->d_xref, B * 12 * (NS + 1) * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_fsteps, B * 12 * N_gait * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_out, B * 24 * NS * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_state, B * MPC_STATE_DOUBLES * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_state_i, B * MPC_STATE_INTS * sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_rho, B * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_info, B * 4 * sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_counter, sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_order, B * sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_gait, B * 4 * N_gait * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMalloc(&h->d_sgait, B * 12 * NS * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMemset(h->d_state, 0, B * MPC_STATE_DOUBLES * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMemset(h->d_state_i, 0, B * MPC_STATE_INTS * sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMemset(h->d_out, 0, B * 24 * NS * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)), qrw_mpc_destroy(h));
+  CUH(cudaMemset(h->d_rho, 0, B * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMallocHost(&h->h_xref, B * 12 * (NS + 1) * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMallocHost(&h->h_fsteps, B * 12 * N_gait * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)), qrw_mpc_destroy(h));
+  CUH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), qrw_mpc_destroy(h));
+  CUH(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming), qrw_mpc_destroy(h));
+  CUH(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES), qrw_mpc_destroy(h));
 #ifdef QRW_AB_KERNELS
-  CU(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES));
-  CU(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES));
-  CU(cudaFuncSetAttribute(mpc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nd::V3_SLAB_BYTES));
+  CUH(cudaFuncSetAttribute(mpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MPC_SLAB_BYTES), qrw_mpc_destroy(h));
+  CUH(cudaFuncSetAttribute(mpc_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta::CTA_SLAB_BYTES), qrw_mpc_destroy(h));
+  CUH(cudaFuncSetAttribute(mpc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nd::V3_SLAB_BYTES), qrw_mpc_destroy(h));
+  CUH(cudaFuncSetAttribute(mpc_v4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v4::V4_SLAB_BYTES), qrw_mpc_destroy(h));
 #endif
   *out = h;
   return 0;
@@ -720,7 +779,13 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
 #ifdef QRW_AB_KERNELS
-  if (h->variant == 3) {
+  if (h->variant == 4) {
+    int grid = 2 * h->sms;
+    if (grid > h->B) grid = h->B;
+    mpc_v4_kernel<<<grid, v4::NT, v4::V4_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, h->sms, d_xref, d_fsteps,
+                                                          h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
+                                                          h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr, nullptr);
+  } else if (h->variant == 3) {
     int grid = 2 * h->sms;
     if (grid > h->B) grid = h->B;
     mpc_v3_kernel<<<grid, nd::NT, nd::V3_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, d_xref, d_fsteps, h->d_state,
@@ -864,8 +929,8 @@ int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter) {
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant) {
   if (!h) return fail("qrw_mpc_set_kernel: null handle");
 #ifdef QRW_AB_KERNELS
-  if (variant < 0 || variant > 3)
-    return fail("qrw_mpc_set_kernel: variant must be 0 (warp per instance), 1 (CTA per instance, v1), 2 (force-first CTA, twisted state chain: default) or 3 (nested-dissection state solve)");
+  if (variant < 0 || variant > 4)
+    return fail("qrw_mpc_set_kernel: variant must be 4 (super-stage chain), 0 (warp per instance), 1 (CTA per instance, v1), 2 (force-first CTA, twisted state chain: default) or 3 (nested-dissection state solve)");
 #else
   if (variant != 2)
     return fail("qrw_mpc_set_kernel: this library contains the one MPC kernel it ships (variant 2); variants 0, 1 and 3 exist only in the A/B "
@@ -933,22 +998,22 @@ int qrw_wbc_create(qrw_wbc_t** out, int batch, int device) {
   h->sms = sm_count_of(device);
   h->C = make_wbc_const();
   const size_t B = (size_t)batch;
-  CU(cudaMalloc(&h->d_M, B * 324 * sizeof(double)));
-  CU(cudaMalloc(&h->d_Jc, B * 216 * sizeof(double)));
-  CU(cudaMalloc(&h->d_f, B * 12 * sizeof(double)));
-  CU(cudaMalloc(&h->d_R, B * 6 * sizeof(double)));
-  CU(cudaMalloc(&h->d_state, B * WBC_STATE_DOUBLES * sizeof(double)));
-  CU(cudaMalloc(&h->d_fres, B * 12 * sizeof(double)));
-  CU(cudaMalloc(&h->d_ddq, B * 6 * sizeof(double)));
-  CU(cudaMalloc(&h->d_H, B * 144 * sizeof(double)));
-  CU(cudaMalloc(&h->d_info, B * 4 * sizeof(int)));
-  CU(cudaMalloc(&h->d_counter, sizeof(int)));
-  CU(cudaMemset(h->d_state, 0, B * WBC_STATE_DOUBLES * sizeof(double)));
-  CU(cudaMemset(h->d_fres, 0, B * 12 * sizeof(double)));
-  CU(cudaMemset(h->d_ddq, 0, B * 6 * sizeof(double)));
-  CU(cudaMemset(h->d_H, 0, B * 144 * sizeof(double)));
-  CU(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)));
-  CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CUH(cudaMalloc(&h->d_M, B * 324 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_Jc, B * 216 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_f, B * 12 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_R, B * 6 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_state, B * WBC_STATE_DOUBLES * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_fres, B * 12 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_ddq, B * 6 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_H, B * 144 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_info, B * 4 * sizeof(int)), qrw_wbc_destroy(h));
+  CUH(cudaMalloc(&h->d_counter, sizeof(int)), qrw_wbc_destroy(h));
+  CUH(cudaMemset(h->d_state, 0, B * WBC_STATE_DOUBLES * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMemset(h->d_fres, 0, B * 12 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMemset(h->d_ddq, 0, B * 6 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMemset(h->d_H, 0, B * 144 * sizeof(double)), qrw_wbc_destroy(h));
+  CUH(cudaMemset(h->d_info, 0, B * 4 * sizeof(int)), qrw_wbc_destroy(h));
+  CUH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), qrw_wbc_destroy(h));
   *out = h;
   return 0;
 }
@@ -1095,20 +1160,20 @@ int qrw_wbctick_create(qrw_wbctick_t** out, int batch, int device) {
   double M[324] = {0.0}, Y[6];
   solo12_base_inertia(Y);
   for (int i = 0; i < 6; ++i) M[i + 18 * i] = Y[i];
-  CU(cudaMemcpy(w->d_M, M, sizeof(M), cudaMemcpyHostToDevice));
+  CUH(cudaMemcpy(w->d_M, M, sizeof(M), cudaMemcpyHostToDevice), qrw_wbctick_destroy(h));
   const size_t sz[13] = {19, 18, 12, 4, 12, 12, 12, 216, 6, 12, 12, 12, 12};
   double** p[13] = {&h->d_q, &h->d_dq, &h->d_f, &h->d_c, &h->d_pg, &h->d_vg, &h->d_ag, &h->d_Jc, &h->d_rnea, &h->d_ddq,
                     &h->d_vdes, &h->d_qdes, &h->d_tau};
   for (int i = 0; i < 13; ++i) {
-    CU(cudaMalloc(p[i], B * sz[i] * sizeof(double)));
-    CU(cudaMemset(*p[i], 0, B * sz[i] * sizeof(double)));
+    CUH(cudaMalloc(p[i], B * sz[i] * sizeof(double)), qrw_wbctick_destroy(h));
+    CUH(cudaMemset(*p[i], 0, B * sz[i] * sizeof(double)), qrw_wbctick_destroy(h));
   }
-  CU(cudaMalloc(&h->d_Yinv, 36 * sizeof(double)));
+  CUH(cudaMalloc(&h->d_Yinv, 36 * sizeof(double)), qrw_wbctick_destroy(h));
   wbc_yinv_kernel<<<1, 32>>>(w->d_M, h->d_Yinv);
   ++g_launches;
-  CU(cudaGetLastError());
-  CU(cudaFuncSetAttribute(wbc_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WT_WARPS * WT_SLAB_BYTES));
-  CU(cudaDeviceSynchronize());
+  CUH(cudaGetLastError(), qrw_wbctick_destroy(h));
+  CUH(cudaFuncSetAttribute(wbc_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WT_WARPS * WT_SLAB_BYTES), qrw_wbctick_destroy(h));
+  CUH(cudaDeviceSynchronize(), qrw_wbctick_destroy(h));
   *out = h;
   return 0;
 }

@@ -41,6 +41,7 @@ struct qrw_mpc_server {
   int* d_k = nullptr;
   double *h_wire = nullptr, *h_out = nullptr;  // pinned staging
   int* h_k = nullptr;
+  unsigned char* seen = nullptr;  // per slot: has this robot been served before?  (its first request is a cold start whatever k it posts)
   long long served = 0, rounds = 0;
 };
 
@@ -54,17 +55,18 @@ int qrw_mpc_server_create(qrw_mpc_server_t** out, qrw_mpc_t* mpc) {
   s->mpc = mpc, s->B = mpc->B;
   s->per_in = 1 + 12 * (NS + 1) + 12 * mpc->N_gait, s->per_out = 24 * NS;
   const size_t B = (size_t)s->B;
-  CU(cudaMalloc(&s->d_wire, B * s->per_in * sizeof(double)));
-  CU(cudaMalloc(&s->d_k, B * sizeof(int)));
-  CU(cudaMallocHost(&s->h_wire, B * s->per_in * sizeof(double)));
-  CU(cudaMallocHost(&s->h_out, B * s->per_out * sizeof(double)));
-  CU(cudaMallocHost(&s->h_k, B * sizeof(int)));
+  CUH(cudaMalloc(&s->d_wire, B * s->per_in * sizeof(double)), qrw_mpc_server_destroy(s));
+  CUH(cudaMalloc(&s->d_k, B * sizeof(int)), qrw_mpc_server_destroy(s));
+  CUH(cudaMallocHost(&s->h_wire, B * s->per_in * sizeof(double)), qrw_mpc_server_destroy(s));
+  CUH(cudaMallocHost(&s->h_out, B * s->per_out * sizeof(double)), qrw_mpc_server_destroy(s));
+  CUH(cudaMallocHost(&s->h_k, B * sizeof(int)), qrw_mpc_server_destroy(s));
   *out = s;
   return 0;
 }
 int qrw_mpc_server_destroy(qrw_mpc_server_t* s) {
   if (!s) return 0;
   cudaFree(s->d_wire), cudaFree(s->d_k), cudaFreeHost(s->h_wire), cudaFreeHost(s->h_out), cudaFreeHost(s->h_k);
+  delete[] s->seen;
   delete s;
   return 0;
 }
@@ -88,10 +90,18 @@ int qrw_mpc_server_poll_host(qrw_mpc_server_t* s, const double* data_in, signed 
   for (int b = 0; b < B; ++b) {
     s->h_k[b] = -1;
     if (__atomic_load_n(&new_data[b], __ATOMIC_ACQUIRE)) {
-      __atomic_store_n(&new_data[b], (signed char)0, __ATOMIC_RELEASE);
-      memcpy(s->h_wire + (size_t)b * s->per_in, data_in + (size_t)b * s->per_in, s->per_in * sizeof(double));
+      // The reference's Arrays are lock-wrapped; here a client that posts AGAIN while its slot is being copied would leave a
+      // torn xref / fsteps.  Clear the flag, copy, and copy again if the flag came back during the copy (the newer post wins).
+      for (int tries = 0; tries < 8; ++tries) {
+        __atomic_store_n(&new_data[b], (signed char)0, __ATOMIC_RELEASE);
+        memcpy(s->h_wire + (size_t)b * s->per_in, data_in + (size_t)b * s->per_in, s->per_in * sizeof(double));
+        if (!__atomic_load_n(&new_data[b], __ATOMIC_ACQUIRE)) break;
+      }
       s->h_k[b] = (int)s->h_wire[(size_t)b * s->per_in];  // int(kf[0]), MPC_Wrapper.py:197
-      if (s->h_k[b] < 0) s->h_k[b] = 0;
+      // a slot's FIRST request is a cold start (create_matrices / osqp_setup) whatever index it carries: a robot attaching
+      // mid-run, or a restarted server, would otherwise run the update path on an all-zero solver state (rho = 0 -> NaN)
+      if (s->h_k[b] < 0 || !s->seen[b]) s->h_k[b] = 0;
+      s->seen[b] = 1;
       ++n;
     }
   }

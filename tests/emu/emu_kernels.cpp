@@ -10,6 +10,7 @@
 #include "../../quadruped-reactive-walking_b200/csrc/mpc_cta_core.cuh"
 #include "../../quadruped-reactive-walking_b200/csrc/mpc_v2_core.cuh"
 #include "../../quadruped-reactive-walking_b200/csrc/mpc_v3_core.cuh"
+#include "../../quadruped-reactive-walking_b200/csrc/mpc_v4_core.cuh"
 
 using namespace qrw;
 
@@ -118,6 +119,33 @@ extern "C" void emu_mpc_v2_run(int B, double dt, int N_gait, int first, int max_
     for (int b = t; b < B; b += nthreads) {
       cta::run_cta(v2::NT, [&]() {
         v2::mpc_v2_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
+                         st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
+                         out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8, 0u);
+      });
+    }
+    if (nthreads <= 1) g_last_slab = slab;
+  };
+  if (nthreads <= 1) {
+    nthreads = 1;
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+    for (auto& t : th) t.join();
+  }
+}
+
+// Super-stage chain CTA kernel core (csrc/mpc_v4_core.cuh), every thread of the 256-thread CTA a fiber; same contract.
+extern "C" void emu_mpc_v4_run(int B, double dt, int N_gait, int first, int max_iter, const double* xref,
+                               const double* fsteps, double* st_d, int* st_i, double* out, int* info, double* rho,
+                               double* dbg, int nthreads) {
+  MpcConst C = make_mpc_const(dt, N_gait);
+  if (max_iter > 0) C.max_iter = max_iter;
+  auto work = [&](int t) {
+    std::vector<double> slab(v4::V4_SLAB_DOUBLES, 0.0);
+    for (int b = t; b < B; b += nthreads) {
+      cta::run_cta(v4::NT, [&]() {
+        v4::mpc_v4_solve(C, slab.data(), xref + (size_t)b * 12 * (NS + 1), fsteps + (size_t)b * 12 * N_gait,
                          st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, first,
                          out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, b % 8, 0u);
       });

@@ -16,7 +16,7 @@ class EmuMPC:
         # "cta": csrc/mpc_cta_core.cuh (256-thread CTA per instance); "warp": csrc/mpc_core.cuh
         # "v2": csrc/mpc_v2_core.cuh (force-first elimination, twisted state chain: the default kernel)
         # "v3": csrc/mpc_v3_core.cuh (force-first elimination, nested-dissection state solve: A/B variant)
-        self.fn = {"v3": emu.emu_mpc_v3_run, "v2": emu.emu_mpc_v2_run, "cta": emu.emu_mpc_cta_run, "warp": emu.emu_mpc_run}[core]
+        self.fn = {"v4": emu.emu_mpc_v4_run, "v3": emu.emu_mpc_v3_run, "v2": emu.emu_mpc_v2_run, "cta": emu.emu_mpc_cta_run, "warp": emu.emu_mpc_run}[core]
         self.std = np.zeros((B, emu.emu_mpc_state_doubles()))
         self.sti = np.zeros((B, emu.emu_mpc_state_ints()), np.int32)
         self.out = np.zeros((B, 384))
