@@ -54,8 +54,9 @@ constexpr int R_MR = 312;  // [6][6]  M = GF D_f B0' E (rows 6..11 x rows 6..11)
 constexpr int SR = 348;
 // tensor-memory columns of a lane quadrant (32-bit columns; a row of 12 doubles = 24 columns)
 constexpr int TM_FI = 0;     // [2][24] row j of F_k^-1 of the thread: warps 0..3 at column 0, warps 4..7 at column 24
-constexpr int TM_ROLE = 48;  // [4][48] the four steps of the chain role of this quadrant's warp, 24 doubles each
-static_assert(TM_ROLE + 4 * 48 <= cta::TMEM_COLS, "tensor-memory columns of a CTA");
+constexpr int TM_ROLE = 48;  // role rows of the quadrant: [0, 96) first role warp (E0 / B0), [96, 192) second (E1 / B1): 4 slots x 12
+                             // doubles per lane; the helper warps H1 / H2 use all 192 columns (8 slots)
+static_assert(TM_ROLE + 192 <= cta::TMEM_COLS, "tensor-memory columns of a CTA");
 constexpr int V_RED = V_REC + 16 * SR;  // 128   reductions
 constexpr int V_INT = V_RED + 128;      // 128 ints
 constexpr int V4_SLAB_DOUBLES = V_INT + 64;
@@ -63,8 +64,9 @@ constexpr int V4_SLAB_BYTES = V4_SLAB_DOUBLES * 8;
 // The four chain warps park their iterates around the chain call.  The park area aliases factorisation scratch that is dead
 // between factorisations: the pivot blocks of super-stages 0..3 (super-stage 4 stays: the middle step reads Sigma_4 from it).
 constexpr int PK = 18;                 // 16 doubles per lane, padded so that the lanes' 16-byte accesses fall on distinct banks
-constexpr int V_PARK = V_SD;           // [4][32][PK]
-static_assert(4 * 32 * PK <= 4 * SB, "the park area overruns the pivot blocks it aliases");
+constexpr int V_PARK = V_SD;           // roles 0..3: [4][32][PK] on the blocks of super-stages 0..3; roles 4, 5: on those of 5, 6
+QRW_HD int park_off(int role) { return role < 4 ? role * 32 * PK : 5 * SB + (role - 4) * 32 * PK; }
+static_assert(4 * 32 * PK <= 4 * SB && 2 * 32 * PK <= 2 * SB, "the park area overruns the pivot blocks it aliases");
 // factorisation scratch inside a record, aliased on the iteration-only vectors [0, 112)
 constexpr int R_Y = 0;   // [12][6] F_k^-1 (D_f B0')(:, rows 6..11); dead after step (c)
 constexpr int R_N = 72;  // [36]    N_k (6x6); dead after step (d)
@@ -339,45 +341,52 @@ QRW_HD void factor(const MpcConst& C, const Sm& S, Regs& R, const RhoSet Rh, dou
     }
     cta::bar();
   }
-  // ---- (f) the four chain warps copy what they walk through in every iteration into their tensor-memory lanes: 24 doubles
-  // per step, [the half on the dependent path | the other half].  Lanes 12..15 of a half-warp duplicate lane 11.
+  // ---- (f) the six chain warps copy what they walk through in every iteration into their tensor-memory lanes, 12 doubles
+  // per slot.  Roles (warp recw + r): 0 = E0, 4 = E1 elimination of the lower / upper half, 1 = B0, 5 = B1 back-substitution,
+  // 2 = H1, 3 = H2 helpers.  In E and B warps lanes 0..11 hold what is on the dependent path, lanes 16..27 the product next
+  // to it (E: one step AHEAD, see state_elim).  Lanes 12..15 of a half-warp duplicate lane 11.
   const int w = tid >> 5, role = (w - recw) & 7;
-  if (role < 4) {
-    const int lane = tid & 31, upi = lane >> 4, i0 = lane & 15, i = i0 < 12 ? i0 : 11;
-    for (int t = 0; t < 4; ++t) {
-      double c0[12], c1[12];
-      const bool live = !(upi && t == 3);  // the upper half has three super-stages next to the middle one
-      if (role == 0) {
-        // elimination: column i of T_t (rows of stage 2t | rows of stage 2t+1)  |  of U_{7-t} (rows of stage 15-2t | 14-2t)
-        const int slot = upi ? 6 - t : t;
-        const double* Tm = S.TT + 288 * (live ? slot : 0) + i;
-        for (int r = 0; r < 12; ++r) {
-          c0[r] = live ? Tm[12 * (upi ? 12 + r : r)] : 0.0;
-          c1[r] = live ? Tm[12 * (upi ? r : 12 + r)] : 0.0;
-        }
-      } else if (role == 1 || role == 2) {
-        // helpers: row i of the first (role 1) / second (role 2) stage of Sigma_t | Sigma_{7-t}
-        const int m = upi ? 7 - t : t;
-        const double* Sr = S.SD + SB * (live ? m : 0) + LS * (12 * (role - 1) + i);
+  if (role < 6) {
+    const int lane = tid & 31, sp = lane >> 4, i0 = lane & 15, i = i0 < 12 ? i0 : 11;
+    const bool up = role >= 4;                       // E1 / B1: the upper half
+    const unsigned tb = tm + TM_ROLE + (up ? 96 : 0);
+    if (role == 0 || role == 4) {
+      for (int t = 0; t < 4; ++t) {
+        double c0[12];
+        // dependent lanes: step t; the lanes next to them: step t + 1.  T_t sits in TT slot t, U_{7-t} in slot 6 - t.
+        const int st = t + sp, nst = up ? 3 : 4;
+        const bool live = st < nst;
+        const double* Tm = S.TT + 288 * (live ? (up ? 6 - st : st) : 0) + i;
+        const int r0 = (up ? !sp : sp) ? 12 : 0;  // lower: dependent rows 0..11, side rows 12..23; upper: the other way round
+        for (int r = 0; r < 12; ++r) c0[r] = live ? Tm[12 * (r0 + r)] : 0.0;
+        cta::tmem_st12(tb + 24 * t, c0);
+      }
+    } else if (role == 1 || role == 5) {
+      for (int u = 0; u < 4; ++u) {
+        double c0[12];
+        const bool live = u < (up ? 3 : 4);
+        // T_{3-u} (slot 3 - u): dependent row i, side row 12 + i  |  U_{5+u} (slot 4 + u): dependent row 12 + i, side row i
+        const double* Tm = S.TT + 288 * (live ? (up ? 4 + u : 3 - u) : 0) + 12 * (((up ? !sp : sp) ? 12 : 0) + i);
+        for (int c = 0; c < 12; ++c) c0[c] = live ? Tm[c] : 0.0;
+        cta::tmem_st12(tb + 24 * u, c0);
+      }
+    } else {
+      // helpers: row i of the first (role 2) / second (role 3) stage of Sigma_t (lanes 0..11) | Sigma_{7-t} (lanes 16..27)
+      for (int t = 0; t < 4; ++t) {
+        double c0[12], c1[12];
+        const bool live = !(sp && t == 3);
+        const double* Sr = S.SD + SB * (live ? (sp ? 7 - t : t) : 0) + LS * (12 * (role - 2) + i);
         cta::lds12(Sr, c0);
         cta::lds12(Sr + 12, c1);
-      } else {
-        // back-substitution: rows i and 12 + i of T_{3-t} (stage 6-2t first)  |  of U_{5+t} (stage 11+2t first)
-        const int slot = upi ? 4 + t : 3 - t;
-        const double* Tm = S.TT + 288 * (live ? slot : 0);
-        for (int c = 0; c < 12; ++c) {
-          c0[c] = live ? Tm[12 * (upi ? 12 + i : i) + c] : 0.0;
-          c1[c] = live ? Tm[12 * (upi ? i : 12 + i) + c] : 0.0;
-        }
+        cta::tmem_st12(tm + TM_ROLE + 48 * t, c0);
+        cta::tmem_st12(tm + TM_ROLE + 48 * t + 24, c1);
       }
-      cta::tmem_st12(tm + TM_ROLE + 48 * t, c0);
-      cta::tmem_st12(tm + TM_ROLE + 48 * t + 24, c1);
     }
   }
   cta::tmem_wait_st();
   // the scratch overlapped CC of the last stage, which nobody writes and the recurrence reads as zero
   if (tid < 12) S.rec[SR * (NS - 1) + R_CC + tid] = 0.0;
-  cta::bar();  // the park area aliases the pivot blocks of super-stages 0..3: nobody reads them after this point
+  cta::bar();  // the park area aliases pivot blocks of super-stages other than 4: nobody reads them after this point
 }
 
 QRW_HD double dot12(const double* m, const double* v) {
@@ -417,127 +426,126 @@ QRW_HD double dot12a(const double* m, const double* v) {
 }
 
 // ------------------------------------------------------------------------------------------
-// The state system per ADMM iteration, FOUR warps.  Lanes 0..11 of a chain warp work on the lower half (super-stages 0..3,
-// stages 0..7), lanes 16..27 on the upper half (super-stages 7..5, stages 15..10); super-stage 4 (stages 8, 9) is the middle.
-// With k0 = 0 | 15 and dk = +1 | -1 for the two halves, step t of the elimination reads s' of stage crit = k0 + 2 t dk (on the
-// dependent path) and s of stage side = crit + dk (an input), and produces s' of stage crit + 2 dk:
-//   E  (warp recw)      elimination, then the middle: X_8 | X_9 = Sigma_4 [s''_8; s''_9]
-//   H1 (warp recw + 1)  v of the first stage of each super-stage:  v = Sigma_m[0:12, :] s'_m      (behind E: named barriers 1, 2)
-//   H2 (warp recw + 2)  v of the second stage:                     v = Sigma_m[12:24, :] s'_m
-//   B  (warp recw + 3)  back-substitution from X_8 | X_9 outwards (waits for E: barrier 4, for H1 / H2: barrier 3)
+// The state system per ADMM iteration, SIX warps.  The lower half (super-stages 0..3, stages 0..7; k0 = 0, dk = +1) and the
+// upper half (super-stages 7..5, stages 15..10; k0 = 15, dk = -1) each have an elimination warp and a back-substitution warp;
+// super-stage 4 (stages 8, 9) is the middle.  Step t of an elimination reads s' of stage crit = k0 + 2 t dk (on the dependent
+// path) and s of stage crit + dk (an input) and produces s' of stage out = crit + 2 dk:
+//     s'_out = s_out - T[side rows]' s_side - T[dependent rows]' s'_crit
+// Lanes 16..27 of the warp form acc = s_out - T[side rows]' s_side ONE STEP AHEAD and leave it in the R_SP slot of the stage;
+// lanes 0..11 take it from there and subtract the dependent product: both half-warps run the same instruction stream (one
+// 12 x 12 product per lane and step, as a step of mpc_v2_core.cuh), only the addresses differ.
+//   E0 / E1 (warps recw, recw + 4)      elimination, then the middle: X_8 (E0) / X_9 (E1) = Sigma_4[row, :] [s''_8; s''_9]
+//   H1 / H2 (warps recw + 2, recw + 3)  v of the first / second stage of each super-stage: v = Sigma_m[rows, :] s'_m
+//   B0 / B1 (warps recw + 1, recw + 5)  back-substitution from X_8 / X_9 outwards; lanes 0..11 the stage the next step needs,
+//                                       lanes 16..27 the stage next to it
+// named barriers: 1, 2 (E0, E1 -> H1, H2: 128), 3 (H1, H2 -> B0, B1: 128), 4 (E0 -> B0: 64), 5 (E0 <-> E1: 64), 6 (E1 -> B1: 64).
 // s' is passed through R_SP, v through R_A, X through R_XT of the stage records, as in mpc_v2_core.cuh.
 // ------------------------------------------------------------------------------------------
-QRW_HDN void state_elim(const double* Sig4, double* rec, int lane, unsigned tmr) {
+template <int UP>
+QRW_HDN void state_elim(const double* Sig4, const double* TTside, double* rec, int lane, unsigned tmr) {
+  constexpr int K0 = (NS - 1) * UP, DK = 1 - 2 * UP, NST = 4 - UP;
   const int i0 = lane & 15;
-  int upi = lane >> 4;
-  cta::opaque(upi);  // keeps ptxas from cloning the chain per half
+  int sp = lane >> 4;  // 0: dependent path, 1: the product next to it
+  cta::opaque(sp);     // keeps ptxas from cloning the chain per half-warp
   const int i = i0 < 12 ? i0 : 11;
   const bool wr = i0 < 12;
-  const int k0 = (NS - 1) * upi, dk = 1 - 2 * upi;
-  cta::TRow tqc, tqs;
-  cta::tmem_ld12(tmr + 24, tqs);  // side half of step 0
-  cta::tmem_ld12(tmr, tqc);       // dependent half of step 0
-  // s' of the stages the elimination does not modify is s itself: 0, 1, 3, 5, 7 | 15, 14, 12, 10 (and 8 | 9 as the start value)
-  {
-    const int kk[5] = {k0, k0 + dk, k0 + 3 * dk, k0 + 5 * dk, k0 + 7 * dk};
+  // per-lane bases: everything below addresses a stage as base + (compile-time stage) * SR
+  const double* bv = rec + R_SP + (sp ? 3 * DK * SR : 0);  // s'_crit of this step | s of the side stage of the NEXT step
+  double* bs = rec + i + (sp ? 2 * DK * SR : 0);            // stage produced by this step | by the next one
+  cta::TRow tq[2];
+  cta::tmem_ld12(tmr, tq[0]);
+  if (!UP) {
+    // s of the odd stages 1, 3, 5, 7 (the even ones and stage 15 come ready from phases (3) / (4))
 #pragma unroll
-    for (int q = 0; q < 5; ++q) {
-      double* r = rec + SR * kk[q];
+    for (int q = 0; q < 2; ++q) {
+      double* r = rec + SR * (1 + 4 * q) + (sp ? 2 * SR : 0);
       const double p = r[R_A + i] + r[R_CC + i];
-      if (wr && !(upi && q == 4)) r[R_SP + i] = p;
+      if (wr) r[R_SP + i] = p;
     }
+    cta::wsync();
   }
-  cta::wsync();
-  double acc;
+  // acc of step 0 (lanes 16..27): the side rows of T_0 | U_7 from shared memory (column i)
   {
     double ts[12], pvs[12];
-    const double* r2 = rec + SR * (k0 + 2 * dk);
-    const double sn = r2[R_A + i] + r2[R_CC + i];
-    cta::lds12(rec + SR * (k0 + dk) + R_SP, pvs);
-    cta::tmem_get12(tqs, ts);
-    acc = sub_dot12(sn, ts, pvs);
+    double* ro = rec + SR * (K0 + 2 * DK);
+    const double sn = UP ? ro[R_A + i] + ro[R_CC + i] : ro[R_SP + i];
+    cta::lds12(rec + SR * (K0 + DK) + R_SP, pvs);
+    cta::lds12c<12>(TTside + i, ts);
+    const double a = sub_dot12(sn, ts, pvs);
+    if (wr && sp) ro[R_SP + i] = a;
   }
 #pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    const int kc = k0 + 2 * t * dk;  // stage whose s' is on the dependent path
-    const int ko = kc + 2 * dk;      // stage produced
-    double pvc[12], tc[12];
+  for (int t = 0; t < NST; ++t) {
+    constexpr int dummy = 0;
+    (void)dummy;
+    const int kc = K0 + 2 * t * DK, ko = kc + 2 * DK;
+    double pv[12], tc[12];
     cta::wsync();
-    if (t == 1) cta::nb_arrive(1, 96);  // s' of super-stages 0, 1 | 7, 6 is in shared memory: the helpers start
-    if (t == 3) cta::nb_arrive(2, 96);  // super-stages 2, 3 | 5
-    cta::lds12(rec + SR * kc + R_SP, pvc);
-    cta::tmem_get12(tqc, tc);
-    if (t < 3) cta::tmem_ld12(tmr + 48 * (t + 1) + 24, tqs);
-    cta::sched_fence();
-    const double p = sub_dot12(acc, tc, pvc);
-    if (wr && !(upi && t == 3)) rec[SR * ko + R_SP + i] = p;
-    if (t < 3) {
-      // the other half of the next step (s of an unmodified stage: an input) in the shadow of the store -> load turnaround
-      double ts[12], pvs[12];
-      cta::tmem_ld12(tmr + 48 * (t + 1), tqc);
-      const double* r2 = rec + SR * (ko + 2 * dk);
-      const double sn = r2[R_A + i] + r2[R_CC + i];
-      cta::lds12(rec + SR * (ko + dk) + R_SP, pvs);
-      cta::tmem_get12(tqs, ts);
-      acc = sub_dot12(sn, ts, pvs);
+    if (t == 1) cta::nb_arrive(1, 128);        // s' of super-stages 0, 1 | 7, 6 is in shared memory
+    if (t == 3 - UP) cta::nb_arrive(2, 128);   // super-stages 2, 3 | 5
+    cta::lds12(bv + SR * kc, pv);
+    double val;
+    if (UP) {  // the upper half produces odd stages: their s is still split into A + CC
+      const double c0 = bs[SR * ko + (sp ? R_A : R_SP)];
+      double c1 = 0.0;
+      if (sp) c1 = bs[SR * ko + R_CC];
+      val = c0 + c1;
+    } else {
+      val = bs[SR * ko + R_SP];
     }
-  }
-  // ---- middle: X_8 (lower lanes) | X_9 (upper lanes) = Sigma_4[row, :] [s''_8; s''_9]
-  {
-    double sg[12], pv[12];
-    const double* Sr = Sig4 + LS * (12 * upi + i);
-    cta::wsync();
-    cta::lds12(Sr + 12, sg);
-    cta::lds12(rec + SR * 9 + R_SP, pv);
-    const double d1 = dot12(sg, pv);
-    cta::lds12(Sr, sg);
-    cta::lds12(rec + SR * 8 + R_SP, pv);
-    const double v = d1 + dot12(sg, pv);
-    if (wr) rec[SR * (8 + upi) + R_XT + i] = v;
+    cta::tmem_get12(tq[t & 1], tc);
+    if (t + 1 < NST) cta::tmem_ld12(tmr + 24 * (t + 1), tq[(t + 1) & 1]);
+    cta::sched_fence();
+    const double p = sub_dot12(val, tc, pv);
+    if (wr && (!sp || t + 1 < NST)) bs[SR * ko + R_SP] = p;
   }
   cta::wsync();
-  cta::nb_arrive(4, 64);  // X_8 and X_9 are in shared memory: the back-substitution warp starts
+  cta::nb_sync(5, 64);  // both halves have stored their side of s''_4
+  // ---- middle: X_8 (E0) | X_9 (E1) = Sigma_4[row, 0:12] s''_8 (lanes 0..11) + Sigma_4[row, 12:24] s''_9 (lanes 16..27)
+  {
+    double sg[12], pv[12];
+    cta::lds12(Sig4 + LS * (12 * UP + i) + 12 * sp, sg);
+    cta::lds12(rec + SR * (8 + sp) + R_SP, pv);
+    double d = dot12(sg, pv);
+    d += cta::shfl_xor(d, 16);
+    if (wr && !sp) rec[SR * (8 + UP) + R_XT + i] = d;
+  }
+  cta::wsync();
+  cta::nb_arrive(UP ? 6 : 4, 64);
 }
 
-// back-substitution: step u reads X of stage src = 8 - 2u | 9 + 2u and produces X of stages src - 2 dk (next step's input) and
-// src - dk
+// back-substitution of one half: step u reads X of stage src = 8 - 2u | 9 + 2u; lanes 0..11 produce X of stage src - 2 dk (the
+// next step's input), lanes 16..27 of stage src - dk
+template <int UP>
 QRW_HDN void state_back(double* rec, int lane, unsigned tmr) {
+  constexpr int DK = 1 - 2 * UP, NST = 4 - UP;
   const int i0 = lane & 15;
-  int upi = lane >> 4;
-  cta::opaque(upi);
+  int sp = lane >> 4;
+  cta::opaque(sp);
   const int i = i0 < 12 ? i0 : 11;
   const bool wr = i0 < 12;
-  const int dk = 1 - 2 * upi;
-  cta::TRow tqc, tqs;
-  cta::tmem_ld12(tmr, tqc);
-  cta::tmem_ld12(tmr + 24, tqs);
-  cta::nb_sync(4, 64);  // the elimination warp has stored X_8 and X_9
+  double* bo = rec + i - (2 - sp) * DK * SR;  // the stage this lane produces, relative to the broadcast stage
+  cta::TRow tq[2];
+  cta::tmem_ld12(tmr, tq[0]);
+  cta::nb_sync(UP ? 6 : 4, 64);  // the elimination warp of this half has stored X_8 | X_9
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
-    const int ks = 8 + upi - 2 * u * dk;  // stage whose X is broadcast
-    const int kc = ks - 2 * dk, kd = ks - dk;
-    const bool live = wr && !(upi && u == 3);
+  for (int u = 0; u < NST; ++u) {
+    const int ks = 8 + UP - 2 * u * DK;
     double xv[12], tr[12];
     if (u > 0) cta::wsync();
     cta::lds12(rec + SR * ks + R_XT, xv);
-    cta::tmem_get12(tqc, tr);
+    cta::tmem_get12(tq[u & 1], tr);
+    if (u + 1 < NST) cta::tmem_ld12(tmr + 24 * (u + 1), tq[(u + 1) & 1]);
     cta::sched_fence();
     const double d = dot12(tr, xv);
-    if (u == 0) cta::nb_sync(3, 96);  // the helpers' v: waited for behind the first product, not in front of it
-    const double X = rec[SR * kc + R_A + i] - d;
-    if (live) rec[SR * kc + R_XT + i] = X;
-    // the stage next to it (not needed by the next step) in the shadow of the store -> load turnaround
-    cta::tmem_get12(tqs, tr);
-    if (u < 3) {
-      cta::tmem_ld12(tmr + 48 * (u + 1), tqc);
-      cta::tmem_ld12(tmr + 48 * (u + 1) + 24, tqs);
-    }
-    const double X2 = rec[SR * kd + R_A + i] - dot12(tr, xv);
-    if (live) rec[SR * kd + R_XT + i] = X2;
+    if (u == 0) cta::nb_sync(3, 128);  // the helpers' v: waited for behind the first product, not in front of it
+    const double X = bo[SR * ks + R_A] - d;
+    if (wr) bo[SR * ks + R_XT] = X;
   }
 }
 
-// helpers: v of the first (which = 0) / second (which = 1) stage of super-stages 0..3 | 7..5, parked in the A slot of the stage
+// helpers: v of the first (which = 0) / second (which = 1) stage of super-stages 0..3 (lanes 0..11) | 7..5 (lanes 16..27),
+// parked in the A slot of the stage
 QRW_HDN void state_helper(double* rec, int lane, unsigned tmr, int which) {
   const int i0 = lane & 15;
   int upi = lane >> 4;
@@ -548,13 +556,13 @@ QRW_HDN void state_helper(double* rec, int lane, unsigned tmr, int which) {
   cta::TRow ta, tb;
   cta::tmem_ld12(tmr, ta);
   cta::tmem_ld12(tmr + 24, tb);
-  cta::nb_sync(1, 96);
+  cta::nb_sync(1, 128);
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
     const int kc = k0 + 2 * t * dk, kn = kc + dk;          // the two stages of the super-stage
     const int kf = upi ? kn : kc, ksn = upi ? kc : kn;       // first and second stage (ascending)
     double m0[12], m1[12], p0[12], p1[12];
-    if (t == 2) cta::nb_sync(2, 96);
+    if (t == 2) cta::nb_sync(2, 128);
     cta::lds12(rec + SR * kf + R_SP, p0);
     cta::lds12(rec + SR * ksn + R_SP, p1);
     cta::tmem_get12(ta, m0);
@@ -567,7 +575,7 @@ QRW_HDN void state_helper(double* rec, int lane, unsigned tmr, int which) {
     if (wr && !(upi && t == 3)) rec[SR * (which ? ksn : kf) + R_A + i] = v;
   }
   cta::wsync();
-  cta::nb_arrive(3, 96);
+  cta::nb_arrive(3, 128);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -905,14 +913,19 @@ QRW_HD void mpc_v4_solve(const MpcConst& C, double* slab, const double* xref, co
       if (j >= 6) wv = wq;
       mk = u1 - Rh.rho_eq * (R.e1 * wv);
       BAk[j] = mk;
-      rec[R_A + j] = C.sigma * R.xX - R.dX * mk;
+      const double ak = C.sigma * R.xX - R.dX * mk;
+      rec[R_A + j] = ak;
+      if (k == NS - 1) rec[R_SP + j] = ak;  // s of the last stage (its CC is zero)
     }
     cta::wsync();
-    // (4) CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage)
+    // (4) CC_{k-1} = D_X^{k-1} A' m_k (record of the previous stage).  An odd stage shares its warp with the stage before it: it
+    // also leaves s_{k-1} = A_{k-1} + CC_{k-1} in the R_SP slot, so that the chain finds s of every EVEN stage ready
     if (isv && k > 0) {
       double v = mk;
       if (j >= 6) v += C.dt * BAk[j - 6];
-      rec[-SR + R_CC + j] = Dk[-SR + 12 + j] * v;
+      const double cc = Dk[-SR + 12 + j] * v;
+      rec[-SR + R_CC + j] = cc;
+      if (k & 1) rec[-SR + R_SP + j] = rec[-SR + R_A + j] + cc;
     }
     cta::bar();
     // The chain is a real call (noinline).  ptxas gives a callee the registers that are dead at the call site; with the
@@ -920,14 +933,16 @@ QRW_HD void mpc_v4_solve(const MpcConst& C, double* slab, const double* xref, co
     // behind the FMAs for want of 12 more (SASS of r02c: one LDS.128 latency per pair of products, 170-220 cycles per
     // step against ~100).  The three chain warps therefore park their iterates in shared memory around the call.
     const int role = (w - recw) & 7;
-    if (role < 4) {
-      double* pk = S.park + (32 * role + l) * PK;
+    if (role < 6) {
+      double* pk = S.park + park_off(role) + l * PK;
       pk[0] = R.xf, pk[1] = R.xX, pk[2] = R.dF, pk[3] = R.dX, pk[4] = R.z1, pk[5] = R.y1, pk[6] = R.e1, pk[7] = R.y2;
       pk[8] = R.zA, pk[9] = R.yA, pk[10] = R.eA, pk[11] = R.zB, pk[12] = R.yB, pk[13] = R.eB, pk[14] = uf, pk[15] = wv;
-      if (role == 0) state_elim(S.SD + SB * 4, S.rec, l, tm + TM_ROLE);
-      else if (role == 1) state_helper(S.rec, l, tm + TM_ROLE, 0);
-      else if (role == 2) state_helper(S.rec, l, tm + TM_ROLE, 1);
-      else state_back(S.rec, l, tm + TM_ROLE);
+      const unsigned tr2 = tm + TM_ROLE + (role >= 4 ? 96 : 0);
+      if (role == 0) state_elim<0>(S.SD + SB * 4, S.TT + 144, S.rec, l, tr2);
+      else if (role == 4) state_elim<1>(S.SD + SB * 4, S.TT + 288 * 6, S.rec, l, tr2);
+      else if (role == 1) state_back<0>(S.rec, l, tr2);
+      else if (role == 5) state_back<1>(S.rec, l, tr2);
+      else state_helper(S.rec, l, tm + TM_ROLE, role - 2);
       R.xf = pk[0], R.xX = pk[1], R.dF = pk[2], R.dX = pk[3], R.z1 = pk[4], R.y1 = pk[5], R.e1 = pk[6], R.y2 = pk[7];
       R.zA = pk[8], R.yA = pk[9], R.eA = pk[10], R.zB = pk[11], R.yB = pk[12], R.eB = pk[13], uf = pk[14], wv = pk[15];
     }

@@ -130,7 +130,8 @@ class BatchedMPC:
 
     def set_kernel(self, variant):
         """2 = the shipped kernel (force-first elimination, twisted state chain, tensor-memory rows).  The A/B test library
-        (tests/ab, -DQRW_AB_KERNELS) also has 3 = nested-dissection state solve, 1 = v1 CTA kernel, 0 = warp per robot."""
+        (tests/ab, -DQRW_AB_KERNELS) also has 4 = super-stage state chain, 3 = nested-dissection state solve, 1 = v1 CTA
+        kernel, 0 = warp per robot."""
         check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
 
     def set_work_order(self, longest_first):

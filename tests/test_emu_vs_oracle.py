@@ -14,7 +14,7 @@ GAITS = ("trot", "walk", "bounding", "pacing", "static")
 from emu_backend import EmuMPC, _p  # noqa: E402
 
 
-@pytest.mark.parametrize("core", ["v2", "cta", "warp"])
+@pytest.mark.parametrize("core", ["v2", "v4", "v3", "cta", "warp"])
 @pytest.mark.parametrize("gaits,seed", [(("trot",), 1), (GAITS, 2)])
 def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
     from qrw_b200 import workloads as wl
@@ -40,7 +40,7 @@ def test_mpc_closed_loop(emu, oracle, gaits, seed, core):
         x0 = ro[:, :12].copy()
 
 
-@pytest.mark.parametrize("core", ["v2", "cta"])
+@pytest.mark.parametrize("core", ["v2", "v4", "v3", "cta"])
 def test_mpc_result_does_not_depend_on_the_thread_schedule(emu, core):
     """Race check without a GPU: between two collectives the emulator may run the threads of a CTA in any order (every order
     is a legal CUDA schedule).  The chain / helper warps of the v2 core hand data over through named barriers; a missing

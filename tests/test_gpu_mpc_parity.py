@@ -72,14 +72,14 @@ def test_the_shipped_library_has_one_mpc_kernel():
 
 
 # ---- A/B build (tests/ab/libqrw_b200_ab.so, -DQRW_AB_KERNELS): the superseded kernels and the nested-dissection experiment
-@pytest.mark.parametrize("kernel", [3, 1, 0])
+@pytest.mark.parametrize("kernel", [4, 3, 1, 0])
 def test_ab_kernels_closed_loop(oracle, ab_library, kernel):
     _closed_loop(oracle, ("trot", "walk", "bounding", "pacing", "static"), B=96, seed=2, ticks=3, kernel=kernel, library=ab_library)
 
 
-@pytest.mark.parametrize("va,vb", [(2, 3), (2, 1), (1, 0)])
+@pytest.mark.parametrize("va,vb", [(2, 4), (2, 3), (2, 1), (1, 0)])
 def test_kernel_variants_agree_at_full_size(ab_library, va, vb):
-    """4096 trot instances, cold tick + one update tick: the kernel variants (2 = shipped, 3 = nested dissection, 1 = v1 CTA,
+    """4096 trot instances, cold tick + one update tick: the kernel variants (2 = shipped, 4 = super-stage chain, 3 = nested dissection, 1 = v1 CTA,
     0 = warp per instance) follow the same iterate sequence (same iteration counts, results equal to round-off)."""
     from qrw_b200 import BatchedMPC, workloads as wl
 
