@@ -79,10 +79,11 @@ int qrw_mpc_info_host(qrw_mpc_t* h, int* iters, int* status, double* rho, int* n
  * (D[384] | E[704] | c | unscaled dynamics bounds[192]) of every instance after the next run */
 int qrw_mpc_set_max_iter(qrw_mpc_t* h, int max_iter);
 int qrw_mpc_debug_host(qrw_mpc_t* h, double* out /* [B][1281] */);
-/* which CUDA kernel runs the solve: 2 (default) = force-first elimination, one 256-thread CTA per instance, matrix rows in
- * tensor memory (mpc_v2_core.cuh); 1 = 24x24 block-tridiagonal CTA kernel (mpc_cta_core.cuh); 0 = one warp per instance
- * (mpc_core.cuh).  1 and 0 are the superseded round-1 kernels kept for A/B parity checks.  All three carry the same
- * persistent state and follow the same OSQP iterate sequence. */
+/* which CUDA kernel runs the solve.  The shipped library contains ONE: 2 = force-first elimination, one 256-thread CTA per
+ * instance, matrix rows in tensor memory (mpc_v2_core.cuh); any other value fails.  The A/B test build of the same source
+ * (-DQRW_AB_KERNELS, tests/ab) also accepts 4 = state chain over super-stages, 3 = nested-dissection state solve, 1 = 24x24
+ * block-tridiagonal CTA kernel, 0 = one warp per instance (superseded / not adopted; same persistent state, same OSQP iterate
+ * sequence). */
 int qrw_mpc_set_kernel(qrw_mpc_t* h, int variant);
 /* work order of the persistent grid (default kernel): 0 (default) = index order; 1 = robots sorted by the ADMM iteration
  * count of their previous solve, longest first (measured on B200: no gain, kept as an A/B hook).  Results do not depend

@@ -20,7 +20,8 @@
 //
 // PARITY UNPINNED: there is no OSQP binary, no OSQP source and no golden vector for these
 // solves in this environment, so this restatement cannot be checked against OSQP itself; it
-// is checked against an independent exact QP solution (tests/test_oracle_qp.py) and against
+// is checked against independent exact QP solutions (tests/test_oracle_pins.py: KKT conditions of
+// random QPs; tests/test_exact_qp.py: an interior-point solve of the assembled MPC QP) and against
 // the analytic anchors of SURVEY.md section 4.
 #pragma once
 #include <algorithm>
@@ -36,8 +37,8 @@ namespace orc {
 // Compressed-sparse-column matrix and triplet conversion.
 // Triplet -> CSC follows the semantics of the reference's vendored converter
 // (src/st_to_cc.cpp:1622 st_to_cc_size, :1675 st_to_cc_index, :1763 st_to_cc_values):
-// entries sorted by (column, row), duplicates summed.  tests/test_st_to_cc_layout.py checks
-// this against the reference converter compiled into oracle/_ref/.
+// entries sorted by (column, row), duplicates summed.  tests/test_oracle_pins.py
+// (test_ml_layout_matches_reference_st_to_cc) checks this against the reference converter compiled into oracle/_ref/.
 // ----------------------------------------------------------------------------------------
 struct Csc {
   int m = 0, n = 0;

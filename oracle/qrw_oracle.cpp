@@ -13,7 +13,7 @@
 // PARITY UNPINNED for everything that goes through OSQP (no OSQP binary/source/golden vector
 // exists here -- see osqp_restated.hpp).  What IS pinned against reference code run here:
 //   * the triplet->CSC value layout of ML (reference src/st_to_cc.cpp compiled into
-//     oracle/_ref/libst_to_cc.so, tests/test_st_to_cc_layout.py, tests/golden/st_to_cc_*.npz)
+//     oracle/_ref/libst_to_cc.so, tests/test_oracle_pins.py::test_ml_layout_matches_reference_st_to_cc)
 //   * the behavioural anchors of scripts/test_mpc.py and the analytic stance forces.
 //
 // Matrix arguments are column-major doubles (what Eigen::MatrixXd::data() holds), one

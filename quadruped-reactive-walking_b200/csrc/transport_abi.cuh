@@ -60,6 +60,7 @@ int qrw_mpc_server_create(qrw_mpc_server_t** out, qrw_mpc_t* mpc) {
   CUH(cudaMallocHost(&s->h_wire, B * s->per_in * sizeof(double)), qrw_mpc_server_destroy(s));
   CUH(cudaMallocHost(&s->h_out, B * s->per_out * sizeof(double)), qrw_mpc_server_destroy(s));
   CUH(cudaMallocHost(&s->h_k, B * sizeof(int)), qrw_mpc_server_destroy(s));
+  s->seen = new unsigned char[B]();
   *out = s;
   return 0;
 }

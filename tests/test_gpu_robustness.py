@@ -60,6 +60,10 @@ def test_non_finite_input_of_one_robot_does_not_touch_its_neighbours(oracle):
     ok = np.arange(B) != 3
     assert np.array_equal(gpu.info()["iters"][ok], cpu.info()["iters"][ok])
     assert_forces_close(rg[ok], rc[ok], "robots next to the one with NaN input")
-    # the robot itself: never reported as solved (OSQP would return an *_INFEASIBLE / NON_CVX status and NaN as well)
-    assert gpu.info()["status"][3] != 1
+    # the robot itself behaves as OSQP v0.6 does on NaN data (the oracle restates it): the inf-norms of the residuals skip NaN
+    # (`if (abs_v_i > max)`), so the first termination check reports "solved" with a NaN solution.  The reference never reads
+    # the status (MPC.cpp:569-599 copies the solution out); what a caller can rely on is that the forces are not finite.
+    cpu.run(0, bad, fs, 4)
     assert not np.isfinite(rg[3]).all()
+    assert gpu.info()["status"][3] == cpu.info()["status"][3]
+    assert gpu.info()["iters"][3] == cpu.info()["iters"][3]
