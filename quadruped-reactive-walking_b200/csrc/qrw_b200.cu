@@ -28,6 +28,7 @@
 #endif
 #include "wbc_core.cuh"
 #include "solo12_core.cuh"
+#include "wbc_tick_core.cuh"
 
 using namespace qrw;
 
@@ -360,154 +361,25 @@ __global__ void __launch_bounds__(128) invkin_kernel(const int B, const double* 
 // Layouts: q [B][19] (xyz, quaternion xyzw, 12 joints), dq [B][18] (base linear and angular velocity in the base
 // frame, 12 joints), contacts [B][4], goals [B][12] (3 x 4 column-major), Jc [B][12*18] column-major.
 // ------------------------------------------------------------------------------------------
-struct BaseState {
-  s12::M3 R;
-  s12::V3 vb, wb;
-};
-__device__ __forceinline__ BaseState load_base(const double* q, const double* dq) {
-  BaseState S;
-  S.R = s12::quat_to_rot(q[3], q[4], q[5], q[6]);
-  S.vb = s12::v3(dq[0], dq[1], dq[2]);
-  S.wb = s12::v3(dq[3], dq[4], dq[5]);
-  return S;
-}
 // One kernel for the whole tick (round 2; round 1 ran pre -> QPWBC -> post as three kernels with Jc / RNEA / ddq handed
-// over through HBM: 3.6 KB per robot on top of 1.24 KB algorithmic).  One WARP per robot, persistent grid pulling robot
-// indices from a counter:
-//   lanes 0..3 (one per leg)  leg kinematics, InvKin, contact-Jacobian rows and the chain's base wrench -> the warp's slab
-//   all lanes                 QPWBC (wbc_solve_instance) reading Jc / RNEA from the slab
-//   lanes 0..3                rnea(q, dq, ddq_cmd + [ddq_res; 0])[6:] - Jc[:, 6:]' f_res
-// The leg code is the register-hungry part (~250 registers when inlined); it is two real calls so that the QPWBC loop, which
-// every lane of the warp spends >90 % of the tick in, is allocated on its own and five 4-warp CTAs fit an SM.
-constexpr int WT_JC = WBC_SLAB_DOUBLES;        // [12 x 18] column-major contact Jacobian
-constexpr int WT_RNEA = WT_JC + 216;           // [6] base wrench of rnea(q, dq, [0; ddq_cmd]) (+ 2 pad)
-constexpr int WT_SLAB_DOUBLES = WT_RNEA + 8;
-constexpr int WT_SLAB_BYTES = WT_SLAB_DOUBLES * 8;
+// over through HBM: 3.6 KB per robot on top of 1.24 KB algorithmic).  A warp takes GROUPS of G = 2, 4 or 8 consecutive
+// robots from a counter (csrc/wbc_tick_core.cuh: the leg code on lanes 4 r + leg, the QP on half-warps with the iterates in
+// registers); what the QP needs of the contact Jacobian (its six base columns) and the base wrench stay in the warp's slab.
 #ifndef QRW_WT_CTAS
-#define QRW_WT_CTAS 4  // measured on B200, 65,536 robots: 3 CTAs/SM 2.37 ms, 4: 2.18 ms, 5 (96 registers: spills) 2.41 ms
+#define QRW_WT_CTAS 4
 #endif
 constexpr int WT_WARPS = 4, WT_CTAS_PER_SM = QRW_WT_CTAS;
-
-__device__ __noinline__ void wbc_tick_pre_leg(const int leg, const double* __restrict__ qb, const double* __restrict__ dqb,
-                                              const double contact_flag, const double* __restrict__ pg,
-                                              const double* __restrict__ vgp, const double* __restrict__ agp, double* Jc_s,
-                                              double* rnea_s, double* ddq_out, double* vdes_out, double* qdes_out) {
-  using namespace s12;
-  double qj[3], dqj[3];
-  for (int c = 0; c < 3; ++c) {
-    qj[c] = qb[7 + 3 * leg + c];
-    dqj[c] = dqb[6 + 3 * leg + c];
-  }
-  const LegKin K = leg_kinematics(leg, qj);
-  V3 J[3], Ji[3];
-  leg_jacobian(K, J);
-  V3 vf, wf, acl;
-  foot_motion(K, dqj, vf, wf, acl);
-  // InvKin::refreshAndCompute for this foot (Kp = 100, Kd = 20, src/InvKin.hpp:56-57)
-  const V3 e = v3(pg[0], pg[1], pg[2]) - K.pf;
-  const V3 vg = v3(vgp[0], vgp[1], vgp[2]);
-  V3 a = 100.0 * e - 20.0 * (vf - vg) + v3(agp[0], agp[1], agp[2]);
-  const bool contact = contact_flag != 0.0;
-  if (contact) a = 0.0 * a;
-  a = a - acl;  // af + wf x vf of InvKin.cpp:48 = classical acceleration of the foot point
-  inv3(J, Ji);
-  const V3 dd = a.x * Ji[0] + (a.y * Ji[1] + a.z * Ji[2]);
-  const V3 dv = vg.x * Ji[0] + (vg.y * Ji[1] + vg.z * Ji[2]);
-  const V3 qs = e.x * Ji[0] + (e.y * Ji[1] + e.z * Ji[2]);
-  const double ddq[3] = {dd.x, dd.y, dd.z};
-  // rnea(q, dq, [0; ddq_cmd]): base wrench
-  const BaseState S = load_base(qb, dqb);
-  const V3 ab = cross(S.wb, S.vb) + S12_GRAVITY * v3(S.R.c0.z, S.R.c1.z, S.R.c2.z);  // R' (0, 0, g)
-  const LegDyn D = leg_dynamics(leg, K, S.wb, v3(0.0, 0.0, 0.0), ab, dqj, ddq);
-  double w6[6] = {D.f.x, D.f.y, D.f.z, D.n.x, D.n.y, D.n.z};
-#pragma unroll
-  for (int c = 0; c < 6; ++c) {  // the four leg lanes of the warp
-    w6[c] += __shfl_xor_sync(0xfu, w6[c], 1);
-    w6[c] += __shfl_xor_sync(0xfu, w6[c], 2);
-  }
-  if (leg == 0) {
-    V3 fb, nb;
-    base_dynamics(S.wb, v3(0.0, 0.0, 0.0), ab, fb, nb);
-    rnea_s[0] = w6[0] + fb.x;
-    rnea_s[1] = w6[1] + fb.y;
-    rnea_s[2] = w6[2] + fb.z;
-    rnea_s[3] = w6[3] + nb.x;
-    rnea_s[4] = w6[4] + nb.y;
-    rnea_s[5] = w6[5] + nb.z;
-  }
-  for (int c = 0; c < 3; ++c) {
-    ddq_out[3 * leg + c] = ddq[c];
-    vdes_out[3 * leg + c] = c == 0 ? dv.x : (c == 1 ? dv.y : dv.z);
-    qdes_out[3 * leg + c] = qj[c] + (c == 0 ? qs.x : (c == 1 ? qs.y : qs.z));
-  }
-  // contact Jacobian rows of this foot (LOCAL_WORLD_ALIGNED, linear part): [R | R (e_c x pf) | R J_leg], zero if swinging
-  double* Jr = Jc_s + 3 * leg;
-  const double on = contact ? 1.0 : 0.0;
-  for (int c = 0; c < 18; ++c) {
-    V3 col = v3(0.0, 0.0, 0.0);
-    if (c < 3)
-      col = c == 0 ? S.R.c0 : (c == 1 ? S.R.c1 : S.R.c2);
-    else if (c < 6) {
-      const V3 ec = v3(c == 3 ? 1.0 : 0.0, c == 4 ? 1.0 : 0.0, c == 5 ? 1.0 : 0.0);
-      col = mul(S.R, cross(ec, K.pf));
-    } else if (c >= 6 + 3 * leg && c < 9 + 3 * leg)
-      col = mul(S.R, J[c - 6 - 3 * leg]);
-    Jr[12 * c] = on * col.x;
-    Jr[12 * c + 1] = on * col.y;
-    Jr[12 * c + 2] = on * col.z;
-  }
-}
-__device__ __noinline__ void wbc_tick_post_leg(const int leg, const double* __restrict__ qb, const double* __restrict__ dqb,
-                                               const double contact_flag, const double* __restrict__ ddq_cmd,
-                                               const double* __restrict__ dr, const double* __restrict__ f_res, double* tau_ff) {
-  using namespace s12;
-  double qj[3], dqj[3], ddq[3];
-  for (int c = 0; c < 3; ++c) {
-    qj[c] = qb[7 + 3 * leg + c];
-    dqj[c] = dqb[6 + 3 * leg + c];
-    ddq[c] = ddq_cmd[3 * leg + c];
-  }
-  const LegKin K = leg_kinematics(leg, qj);
-  V3 J[3];
-  leg_jacobian(K, J);
-  const BaseState S = load_base(qb, dqb);
-  const V3 ab = v3(dr[0], dr[1], dr[2]) + cross(S.wb, S.vb) + S12_GRAVITY * v3(S.R.c0.z, S.R.c1.z, S.R.c2.z);
-  const LegDyn D = leg_dynamics(leg, K, S.wb, v3(dr[3], dr[4], dr[5]), ab, dqj, ddq);
-  const double* fr = f_res + 3 * leg;
-  const V3 fl = (contact_flag != 0.0) ? mulT(S.R, v3(fr[0], fr[1], fr[2])) : v3(0.0, 0.0, 0.0);  // R' f
-  for (int c = 0; c < 3; ++c) tau_ff[3 * leg + c] = D.tau[c] - dot(J[c], fl);
-}
 __global__ void __launch_bounds__(32 * WT_WARPS, WT_CTAS_PER_SM)
-    wbc_tick_kernel(const WbcConst C, const int B, const int first, const double* __restrict__ q, const double* __restrict__ dq,
-                    const double* __restrict__ f_cmd, const int f_stride, const double* __restrict__ contacts,
-                    const double* __restrict__ pgoals, const double* __restrict__ vgoals, const double* __restrict__ agoals,
-                    const double* __restrict__ M, const double* __restrict__ Yinv, double* st, double* f_res, double* ddq_res,
-                    int* info, double* ddq_cmd, double* vdes, double* qdes, double* tau_ff, double* Jc_dbg, double* rnea_dbg,
-                    int* counter) {
+    wbc_tick_kernel(const WbcConst C, const int B, const int G, const int first, const wt::TickIo io, int* counter) {
   extern __shared__ __align__(16) double slab[];
-  double* sl = slab + (threadIdx.x >> 5) * WT_SLAB_DOUBLES;
+  double* sl = slab + (threadIdx.x >> 5) * wt::WT2_SLAB_DOUBLES;
   const int lane = threadIdx.x & 31;
   for (;;) {
-    int bi = 0;
-    if (lane == 0) bi = atomicAdd(counter, 1);
-    bi = __shfl_sync(0xffffffffu, bi, 0);
-    if (bi >= B) break;
-    const size_t b = (size_t)bi;
-    const double *qb = q + b * 19, *dqb = dq + b * 18;
-    if (lane < 4)
-      wbc_tick_pre_leg(lane, qb, dqb, contacts[b * 4 + lane], pgoals + b * 12 + 3 * lane, vgoals + b * 12 + 3 * lane,
-                       agoals + b * 12 + 3 * lane, sl + WT_JC, sl + WT_RNEA, ddq_cmd + b * 12, vdes + b * 12, qdes + b * 12);
-    __syncwarp();
-    if (Jc_dbg) {  // parity tests read the intermediates; the product path leaves them on chip
-      for (int e = lane; e < 216; e += 32) Jc_dbg[b * 216 + e] = sl[WT_JC + e];
-      if (lane < 6) rnea_dbg[b * 6 + lane] = sl[WT_RNEA + lane];
-    }
-    wbc_solve_instance(C, sl, M, sl + WT_JC, f_cmd + b * (size_t)f_stride, sl + WT_RNEA, st + b * WBC_STATE_DOUBLES, first,
-                       f_res + b * 12, ddq_res + b * 6, nullptr, info + 4 * b, Yinv);
-    __syncwarp();  // f_res / ddq_res / ddq_cmd written by other lanes of this warp are visible to the leg lanes
-    if (lane < 4)
-      wbc_tick_post_leg(lane, qb, dqb, contacts[b * 4 + lane], ddq_cmd + b * 12, ddq_res + b * 6, f_res + b * 12, tau_ff + b * 12);
-    __syncwarp();
+    int b0 = 0;
+    if (lane == 0) b0 = atomicAdd(counter, G);
+    b0 = __shfl_sync(0xffffffffu, b0, 0);
+    if (b0 >= B) break;
+    wt::tick_group(C, B, G, first, io, sl, lane, b0);
   }
 }
 // pinv(M[:6, :6]) of the batch-wide M, once per handle (same code as the per-robot path: bit-identical)
@@ -1172,7 +1044,7 @@ int qrw_wbctick_create(qrw_wbctick_t** out, int batch, int device) {
   wbc_yinv_kernel<<<1, 32>>>(w->d_M, h->d_Yinv);
   ++g_launches;
   CUH(cudaGetLastError(), qrw_wbctick_destroy(h));
-  CUH(cudaFuncSetAttribute(wbc_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WT_WARPS * WT_SLAB_BYTES), qrw_wbctick_destroy(h));
+  CUH(cudaFuncSetAttribute(wbc_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WT_WARPS * wt::WT2_SLAB_BYTES), qrw_wbctick_destroy(h));
   CUH(cudaDeviceSynchronize(), qrw_wbctick_destroy(h));
   *out = h;
   return 0;
@@ -1203,13 +1075,16 @@ int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, 
   cudaStream_t s = (cudaStream_t)stream;
   qrw_wbc* w = h->wbc;
   CU(cudaMemsetAsync(w->d_counter, 0, sizeof(int), s));
-  int grid = WT_CTAS_PER_SM * w->sms;  // persistent: 5 CTAs x 4 warps x 9.7 KB per SM
-  const int need = (h->B + WT_WARPS - 1) / WT_WARPS;
+  // group size: eight robots per warp keep every lane of the leg code busy; a batch too small to fill the GPU's warps that way
+  // takes smaller groups (more warps in flight, a shorter critical path per warp)
+  const int slots = WT_CTAS_PER_SM * w->sms * WT_WARPS;
+  const int G = h->B >= 8 * slots ? 8 : (h->B >= 4 * slots ? 4 : 2);
+  int grid = WT_CTAS_PER_SM * w->sms;  // persistent
+  const int need = ((h->B + G - 1) / G + WT_WARPS - 1) / WT_WARPS;
   if (grid > need) grid = need;
-  wbc_tick_kernel<<<grid, 32 * WT_WARPS, WT_WARPS * WT_SLAB_BYTES, s>>>(
-      w->C, h->B, w->first ? 1 : 0, q, dq, f_cmd, w->f_stride, contacts, pgoals, vgoals, agoals, w->d_M, h->d_Yinv, w->d_state,
-      w->d_fres, w->d_ddq, w->d_info, h->d_ddq, h->d_vdes, h->d_qdes, h->d_tau, h->debug ? h->d_Jc : nullptr,
-      h->debug ? h->d_rnea : nullptr, w->d_counter);
+  wt::TickIo io{q, dq, f_cmd, contacts, pgoals, vgoals, agoals, h->d_Yinv, w->f_stride, w->d_state, w->d_fres, w->d_ddq, w->d_info,
+                h->d_ddq, h->d_vdes, h->d_qdes, h->d_tau, h->debug ? h->d_Jc : nullptr, h->debug ? h->d_rnea : nullptr};
+  wbc_tick_kernel<<<grid, 32 * WT_WARPS, WT_WARPS * wt::WT2_SLAB_BYTES, s>>>(w->C, h->B, G, w->first ? 1 : 0, io, w->d_counter);
   ++g_launches;
   CU(cudaGetLastError());
   w->first = false;  // QPWBC::initialized, src/QPWBC.cpp:23,254

@@ -73,6 +73,32 @@ namespace cta {
 __device__ __forceinline__ int tid() { return (int)threadIdx.x; }
 __device__ __forceinline__ void bar() { __syncthreads(); }
 __device__ __forceinline__ void wsync() { __syncwarp(); }
+// 64-bit shuffles as two 32-bit ones on an explicitly unpacked pair: the built-in double overload leaves ptxas with the halves
+// in swapped registers and three XORs per shuffle to put them back (seen in the SASS of the whole-body tick kernel)
+__device__ __forceinline__ double shfl_idx64(double v, int src, int clamp) {
+  double r;
+  asm volatile(
+      "{ .reg .b32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "shfl.sync.idx.b32 lo, lo, %2, %3, 0xffffffff;\n\t"
+      "shfl.sync.idx.b32 hi, hi, %2, %3, 0xffffffff;\n\t"
+      "mov.b64 %0, {lo, hi}; }"
+      : "=d"(r)
+      : "d"(v), "r"(src), "r"(clamp));
+  return r;
+}
+__device__ __forceinline__ double shfl_bfly64(double v, int m) {
+  double r;
+  asm volatile(
+      "{ .reg .b32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "shfl.sync.bfly.b32 lo, lo, %2, 0x1f, 0xffffffff;\n\t"
+      "shfl.sync.bfly.b32 hi, hi, %2, 0x1f, 0xffffffff;\n\t"
+      "mov.b64 %0, {lo, hi}; }"
+      : "=d"(r)
+      : "d"(v), "r"(m));
+  return r;
+}
 __device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 // max over the warp, result on every lane
 __device__ __forceinline__ double warp_max(double v) {
@@ -86,9 +112,14 @@ __device__ __forceinline__ void gather12(double v, double* out) {
   for (int j = 0; j < 12; ++j) out[j] = __shfl_sync(0xffffffffu, v, j);
 }
 __device__ __forceinline__ int fetch_add(int* p, int v) { return atomicAdd(p, v); }
+// true on every lane of the warp if the predicate holds on any of them
+__device__ __forceinline__ bool any(bool p) { return __any_sync(0xffffffffu, p) != 0; }
 // value held by lane `src` (0..15) of the caller's 16-lane group
 __device__ __forceinline__ double shfl16(double v, int src) { return __shfl_sync(0xffffffffu, v, src, 16); }
 __device__ __forceinline__ double shfl_xor(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+// the same two on the explicitly unpacked pair (whole-body tick)
+__device__ __forceinline__ double hshfl(double v, int src) { return shfl_idx64(v, src, 0x101f); }
+__device__ __forceinline__ double hxor(double v, int m) { return shfl_bfly64(v, m); }
 // v[0..11] = p[0..11] from shared memory (16-byte aligned) as six LDS.128 issued back to back: volatile, so
 // that ptxas keeps them together ahead of their consumers instead of serialising load -> FMA -> load.
 __device__ __forceinline__ void lds12(const double* p, double* v) {
@@ -229,8 +260,11 @@ double shfl(double v, int src);
 double warp_max(double v);
 void gather12(double v, double* out);
 int fetch_add(int* p, int v);
+bool any(bool p);
 double shfl16(double v, int src);
 double shfl_xor(double v, int m);
+inline double hshfl(double v, int src) { return shfl16(v, src); }
+inline double hxor(double v, int m) { return shfl_xor(v, m); }
 inline void sched_fence() {}
 inline void opaque(int&) {}
 void nb_arrive(int id, int nthreads);

@@ -195,6 +195,16 @@ inline void gather12(double v, double* out) {
   for (int j = 0; j < 12; ++j) out[j] = e->xch[w0 + j];
   wsync();
 }
+inline bool any(bool p) {
+  Emu* e = g_emu;
+  const int t = e->cur, w0 = t & ~31;
+  e->xch[t] = p ? 1.0 : 0.0;
+  wsync();
+  bool r = false;
+  for (int i = 0; i < 32 && w0 + i < e->n; ++i) r = r || e->xch[w0 + i] != 0.0;
+  wsync();
+  return r;
+}
 inline double shfl16(double v, int src) {
   Emu* e = g_emu;
   const int t = e->cur;

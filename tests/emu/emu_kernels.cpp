@@ -186,3 +186,31 @@ extern "C" void emu_mpc_v3_run(int B, double dt, int N_gait, int first, int max_
     for (auto& t : th) t.join();
   }
 }
+
+// ---- the whole-body tick, groups of G robots per emulated warp (csrc/wbc_tick_core.cuh)
+#include "../../quadruped-reactive-walking_b200/csrc/wbc_tick_core.cuh"
+extern "C" void emu_wbc_tick_run(int B, int G, int first, const double* q, const double* dq, const double* f_cmd, int f_stride,
+                                 const double* contacts, const double* pgoals, const double* vgoals, const double* agoals,
+                                 const double* M, double* st, double* f_res, double* ddq_res, int* info, double* ddq_cmd,
+                                 double* vdes, double* qdes, double* tau_ff, double* Jc_dbg, double* rnea_dbg) {
+  WbcConst C = make_wbc_const();
+  double Y[36], Yinv[36], U[36], V[36];
+  for (int e = 0; e < 36; ++e) Y[e] = M[(e % 6) + 18 * (e / 6)];
+  pinv6_serial(Y, Yinv, U, V);
+  wt::TickIo io{q, dq, f_cmd, contacts, pgoals, vgoals, agoals, Yinv, f_stride, st, f_res, ddq_res, info,
+                ddq_cmd, vdes, qdes, tau_ff, Jc_dbg, rnea_dbg};
+  const int warps = 2;  // two emulated warps per CTA, as the kernel has several
+  std::vector<double> slab((size_t)warps * wt::WT2_SLAB_DOUBLES, 0.0);
+  int counter = 0;
+  cta::run_cta(32 * warps, [&]() {
+    const int tid = cta::tid(), lane = tid & 31;
+    double* sl = slab.data() + (size_t)(tid >> 5) * wt::WT2_SLAB_DOUBLES;
+    for (;;) {
+      int b0 = 0;
+      if (lane == 0) b0 = cta::fetch_add(&counter, G);
+      b0 = (int)cta::shfl((double)b0, 0);
+      if (b0 >= B) break;
+      wt::tick_group(C, B, G, first, io, sl, lane, b0);
+    }
+  });
+}

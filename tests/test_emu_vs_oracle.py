@@ -182,3 +182,70 @@ def test_invkin(emu, oracle):
     emu.emu_invkin_run(B, *[_p(a) for a in args], *[_p(o) for o in outs])
     for a, b in zip(outs, oracle.invkin(*args)):
         np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-12)
+
+
+def _emu_wbc_tick(emu, B, G, first, args, st, M):
+    q, dq, f, contacts, pg, vg, ag = [np.ascontiguousarray(a, np.float64) for a in args]
+    out = dict(f_res=np.zeros((B, 12)), ddq_res=np.zeros((B, 6)), info=np.zeros((B, 4), np.int32), ddq_cmd=np.zeros((B, 12)),
+               vdes=np.zeros((B, 12)), qdes=np.zeros((B, 12)), tau_ff=np.zeros((B, 12)), Jc=np.zeros((B, 216)), RNEA=np.zeros((B, 6)))
+    emu.emu_wbc_tick_run(B, G, int(first), _p(q), _p(dq), _p(f), 12, _p(contacts), _p(pg), _p(vg), _p(ag), _p(M), _p(st),
+                         _p(out["f_res"]), _p(out["ddq_res"]), _p(out["info"]), _p(out["ddq_cmd"]), _p(out["vdes"]), _p(out["qdes"]),
+                         _p(out["tau_ff"]), _p(out["Jc"]), _p(out["RNEA"]))
+    return out
+
+
+def _wbc_tick_M(oracle):
+    q0 = np.zeros(19)
+    q0[6] = 1.0
+    M = oracle.solo12_crba(q0)
+    M[:6, :6] = M[:6, :6] * np.eye(6)  # scripts/QP_WBC.py:93
+    return np.asfortranarray(M).ravel(order="F").copy()
+
+
+@pytest.mark.parametrize("G,B", [(8, 37), (4, 22), (2, 9)])
+def test_wbc_tick_groups_three_calls(emu, oracle, G, B):
+    """csrc/wbc_tick_core.cuh (eight / four / two robots per warp, the QP on half-warps) in the fiber emulation against the
+    oracle's composition of wbc_controller.compute; ragged batches (the last group is partly empty), warm start over three calls."""
+    from qrw_b200 import workloads as wl
+
+    cpu = oracle.OracleWBC(B)
+    st = np.zeros((B, emu.emu_wbc_state_doubles()))
+    M = _wbc_tick_M(oracle)
+    for call in range(3):
+        args = wl.wbc_tick_inputs(B, seed=40 + call, level_base=(call != 1))
+        got = _emu_wbc_tick(emu, B, G, call == 0, args, st, M)
+        ref = oracle.wbc_tick(cpu, *args, nthreads=4)
+        np.testing.assert_allclose(got["Jc"], ref["Jc"], rtol=1e-11, atol=1e-11)
+        np.testing.assert_allclose(got["RNEA"], ref["RNEA"], rtol=1e-10, atol=1e-10)
+        np.testing.assert_allclose(got["ddq_cmd"], ref["ddq_cmd"], rtol=1e-9, atol=1e-8)
+        np.testing.assert_allclose(got["qdes"], ref["qdes"], rtol=1e-10, atol=1e-10)
+        np.testing.assert_allclose(got["vdes"], ref["vdes"], rtol=1e-10, atol=1e-10)
+        assert np.array_equal(got["info"][:, 0], cpu.info()["iters"]), f"call {call}"
+        assert_forces_close(got["f_res"], ref["f_res"], f"f_res call {call}")
+        np.testing.assert_allclose(got["ddq_res"], ref["ddq_res"], rtol=1e-5, atol=1e-4)
+        np.testing.assert_allclose(got["tau_ff"], ref["tau_ff"], rtol=1e-5, atol=1e-4)
+
+
+def test_wbc_tick_groups_do_not_depend_on_the_thread_schedule_or_the_group_size(emu, oracle):
+    """Five legal schedules of the emulated threads and the three group sizes give the same bits: no race between the
+    collectives, and a robot's result does not depend on who shares its warp."""
+    from qrw_b200 import workloads as wl
+
+    B = 19
+    M = _wbc_tick_M(oracle)
+    res = []
+    try:
+        for order, G in ((0, 8), (1, 8), (2, 8), (3, 4), (4, 2)):
+            emu.emu_set_schedule(order)
+            st = np.zeros((B, emu.emu_wbc_state_doubles()))
+            got = []
+            for call in range(2):
+                o = _emu_wbc_tick(emu, B, G, call == 0, wl.wbc_tick_inputs(B, seed=50 + call, level_base=False), st, M)
+                got.append([o[k].copy() for k in sorted(o)] + [st.copy()])
+            res.append(got)
+    finally:
+        emu.emu_set_schedule(0)
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y)
