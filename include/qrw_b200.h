@@ -164,6 +164,9 @@ int qrw_wbctick_run_ctrl_device(qrw_wbctick_t* h, double h_ref, const double* vr
 /* intermediates handed to QPWBC (Jc [B][216], RNEA [B][6]) and its ddq_res [B][6]; any pointer may be NULL.  Jc / RNEA stay
  * on the SM unless qrw_wbctick_set_debug(h, 1) was called before the tick (they are then copied to HBM as well). */
 int qrw_wbctick_set_debug(qrw_wbctick_t* h, int on);
+/* robots per warp of the tick kernel (csrc/wbc_tick_core.cuh): 2, 4 or 8; 0 (default) = chosen at launch from the batch
+ * size.  A tuning knob only: results do not depend on it. */
+int qrw_wbctick_set_group(qrw_wbctick_t* h, int group);
 int qrw_wbctick_debug_host(qrw_wbctick_t* h, double* Jc, double* rnea6, double* ddq_res);
 /* diag(crba(q = 0)[:6, :6]): (m, m, m, Ixx, Iyy, Izz) of the whole robot about the base frame */
 int qrw_solo12_base_inertia(double* Y6);

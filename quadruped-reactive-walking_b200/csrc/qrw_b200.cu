@@ -497,6 +497,7 @@ struct qrw_wbctick {
   double *d_Jc = nullptr, *d_rnea = nullptr, *d_ddq = nullptr, *d_vdes = nullptr, *d_qdes = nullptr, *d_tau = nullptr;
   double* d_Yinv = nullptr;  // pinv(M[:6, :6]) of the batch-wide M
   bool debug = false;        // copy Jc / RNEA out of the kernel (parity tests); off: they never leave the SM
+  int group = 0;             // robots per warp (2, 4, 8); 0 = chosen from the batch size at launch
 };
 
 // diag of crba(q = 0)[:6, :6] (scripts/QP_WBC.py:89-93): total mass, and the moments of inertia of the whole robot
@@ -1055,6 +1056,14 @@ int qrw_wbctick_set_debug(qrw_wbctick_t* h, int on) {
   h->debug = on != 0;
   return 0;
 }
+// Robots per warp of the tick kernel: 2, 4 or 8; 0 (default) = chosen at launch from the batch size (8 once that fills every
+// warp the GPU can hold, smaller groups for small batches).  Results do not depend on it.
+int qrw_wbctick_set_group(qrw_wbctick_t* h, int group) {
+  if (!h) return fail("qrw_wbctick_set_group: null handle");
+  if (group != 0 && group != 2 && group != 4 && group != 8) return fail("qrw_wbctick_set_group: group must be 0, 2, 4 or 8");
+  h->group = group;
+  return 0;
+}
 int qrw_wbctick_destroy(qrw_wbctick_t* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
@@ -1078,7 +1087,7 @@ int qrw_wbctick_run_device(qrw_wbctick_t* h, const double* q, const double* dq, 
   // group size: eight robots per warp keep every lane of the leg code busy; a batch too small to fill the GPU's warps that way
   // takes smaller groups (more warps in flight, a shorter critical path per warp)
   const int slots = WT_CTAS_PER_SM * w->sms * WT_WARPS;
-  const int G = h->B >= 8 * slots ? 8 : (h->B >= 4 * slots ? 4 : 2);
+  const int G = h->group ? h->group : (h->B >= 8 * slots ? 8 : (h->B >= 4 * slots ? 4 : 2));
   int grid = WT_CTAS_PER_SM * w->sms;  // persistent
   const int need = ((h->B + G - 1) / G + WT_WARPS - 1) / WT_WARPS;
   if (grid > need) grid = need;

@@ -244,9 +244,11 @@ QRW_HD void solve_pair(const WbcConst& C, double* ps, const int hl, const bool v
     if (isv) ps[P_V1 + j] = L.D;
     cta::wsync();
     cta::lds12(ps + P_V1, Dv);
+    // max_i |(cscale D_i h_i) D_j| = (max_i |cscale D_i h_i|) D_j to the bit: D_j > 0 and rounding is monotone
     double nrm = 0.0;
 #pragma unroll
-    for (int i = 0; i < 12; ++i) nrm = amax(nrm, cscale * Dv[i] * hc[i] * L.D);
+    for (int i = 0; i < 12; ++i) nrm = amax(nrm, cscale * Dv[i] * hc[i]);
+    nrm *= L.D;
     const double eA0 = cta::hshfl(L.eA, 3 * f), eB0 = cta::hshfl(L.eB, 3 * f);
     const double eA1 = cta::hshfl(L.eA, 3 * f + 1), eB1 = cta::hshfl(L.eB, 3 * f + 1);
     const double Dz = cta::hshfl(L.D, 3 * f + 2);
@@ -275,7 +277,8 @@ QRW_HD void solve_pair(const WbcConst& C, double* ps, const int hl, const bool v
     cta::lds12(ps + P_V2, Dv);
     double n2 = 0.0;
 #pragma unroll
-    for (int i = 0; i < 12; ++i) n2 = amax(n2, cscale * Dv[i] * hc[i] * L.D);
+    for (int i = 0; i < 12; ++i) n2 = amax(n2, cscale * Dv[i] * hc[i]);
+    n2 *= L.D;
     if (isv) ps[P_V0 + j] = n2;
     double qn = hmax16(fabs(cscale * L.D * qold));
     cta::wsync();
@@ -306,6 +309,7 @@ QRW_HD void solve_pair(const WbcConst& C, double* ps, const int hl, const bool v
   // ---- ADMM.  The two halves of the warp iterate in lockstep; a half that has terminated keeps its iterates frozen.
   int status = -10, iter_done = 0;
   bool act = true;
+  int until_check = C.check_every, until_adapt = C.adapt_every;  // countdowns instead of iter % n (20 instructions each)
 #pragma unroll 1
   for (int iter = 1; iter <= C.max_iter; ++iter) {
     const double wA = L.eA * (L.rrA * L.zA - L.yA);
@@ -345,7 +349,9 @@ QRW_HD void solve_pair(const WbcConst& C, double* ps, const int hl, const bool v
       }
     }
     if (act) L.x = C.alpha * xt + (1.0 - C.alpha) * L.x;
-    if (iter % C.check_every == 0) {
+    --until_adapt;
+    if (--until_check == 0) {
+      until_check = C.check_every;
       // residuals (auxil.c compute_pri_res / compute_dua_res / compute_*_tol)
       cta::wsync();
       if (isv) ps[P_V0 + j] = L.x;
@@ -381,7 +387,8 @@ QRW_HD void solve_pair(const WbcConst& C, double* ps, const int hl, const bool v
           status = (pri_u < 10.0 * C.eps_abs + 10.0 * C.eps_rel * rel_p && dua_u < 10.0 * C.eps_abs + 10.0 * C.eps_rel * rel_d) ? 2 : -2;
         }
       }
-      if (iter % C.adapt_every == 0) {
+      if (until_adapt <= 0 && iter % C.adapt_every == 0) {
+        until_adapt = C.adapt_every;
         // the scaled norms are needed for the rho estimate only
         double pri_s = amax(fabs(rsA), rsB);
         double np_s = amax(amax(amax(fabs(L.zA), L.zB), axA), axB);

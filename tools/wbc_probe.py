@@ -8,9 +8,11 @@ from qrw_b200 import _lib
 _lib._SO = os.environ.get("QRW_LIB", _lib._SO)
 from qrw_b200 import BatchedWbcTick, workloads as wl
 
-B = 65536
+B = int(os.environ.get("WBC_B", "65536"))
 dev = torch.device("cuda", 0)
 tick = BatchedWbcTick(B)
+if os.environ.get("WBC_G"):
+    _lib.check(tick._L.qrw_wbctick_set_group(tick._h, int(os.environ["WBC_G"])))
 targs = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in wl.wbc_tick_inputs(B, seed=3)]
 for _ in range(3):
     tick.compute(*targs)
@@ -23,4 +25,4 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 10
 it = np.empty(B, np.int32)
-print(f"{os.path.basename(_lib._SO)}: {ms:.3f} ms per tick of {B} robots = {B / ms / 1e3:.1f} M ticks/s")
+print(f"{os.path.basename(_lib._SO)} G={os.environ.get('WBC_G', 'auto')}: {ms:.3f} ms per tick of {B} robots = {B / ms / 1e3:.1f} M ticks/s")
