@@ -51,6 +51,10 @@ BYTES_PER_SOLVE = 35340  # in 3,556 + out 3,080 + warm-start state
 # (profiles/r02p_ncu_mpc_v2.txt: 88.68 MB + 46.30 MB), per robot: no re-reads beyond the algorithmic bytes
 NCU_DRAM_BYTES_PER_SOLVE = (88.682752e6 + 46.301696e6) / 4096
 DFMA_PEAK_TFLOPS = 34.20  # profiles/r02_fp64_bench.txt (tools/fp64_bench.cu on this pool's B200; cuBLAS DGEMM 8192^3: 35.76)
+# FP64 operations one whole-body tick executes (2 x DFMA + DADD + DMUL thread instructions of one wbc_tick_kernel launch over
+# 65,536 robots, ncu --set full, profiles/r02s_ncu_wbc_tick.txt: 1.727 G DFMA, 0.692 G DADD, 1.589 G DMUL): the kernel is
+# instruction-bound on the FP64 pipe (44 % active), so this is the bound its fraction is quoted against
+WBC_FLOP_PER_TICK = (2 * 1.7271e9 + 0.6917e9 + 1.5890e9) / 65536
 ALL_GAITS = ("trot", "walk", "bounding", "pacing", "static")
 CONFIGS = {
     2: dict(metric="Solo12 MPC QP solves/sec (batched, 16-step)", unit="solves/s", batch=4096, total=None, gaits=("trot",),
@@ -481,6 +485,10 @@ def aux_legs(args, L, dev, local, rank, world, B, K, W, Bw, mpc, snap, dev_in, r
                        "kernels_per_step": int(getattr(tick, "kernels_per_tick", 3)),
                        "hbm_GBps_algorithmic": wbc_bytes * Bw / (wbc_ms * 1e-3) / 1e9,
                        "hbm_frac_of_measured": wbc_bytes * Bw / (wbc_ms * 1e-3) / 1e9 / hbm,
+                       "roofline": {"bound": "fp64_dfma", "achieved": WBC_FLOP_PER_TICK * Bw / (wbc_ms * 1e-3) / 1e12, "peak": DFMA_PEAK_TFLOPS,
+                                    "unit": "TFLOP/s", "frac": WBC_FLOP_PER_TICK * Bw / (wbc_ms * 1e-3) / 1e12 / DFMA_PEAK_TFLOPS,
+                                    "kernel": "wbc_tick_kernel", "flop_per_tick": WBC_FLOP_PER_TICK,
+                                    "flop_source": "executed FP64 thread instructions of one launch (ncu), see bench.py WBC_FLOP_PER_TICK"},
                        "workload": "BASELINE config 4: Solo12 kinematics/RNEA + InvKin + QPWBC + tau_ff, inputs resident in HBM"}
     del tick
     # full control tick on the MPC batch: MPC update solve, then the whole-body tick with f_cmd read in place from the result
@@ -527,6 +535,9 @@ def aux_legs(args, L, dev, local, rank, world, B, K, W, Bw, mpc, snap, dev_in, r
     aux["planner_tick"] = {"value": world * Bw / (plan_ms * 1e-3), "unit": "ticks/s", "robots_per_gpu": Bw, "ms_per_step": plan_ms,
                            "kernels_per_step": 1, "hbm_GBps_algorithmic": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9,
                            "hbm_frac_of_measured": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9 / hbm,
+                           "roofline": {"bound": "hbm", "achieved": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                                        "frac": plan_bytes * Bw / (plan_ms * 1e-3) / 1e9 / hbm, "kernel": "planner_tick_kernel",
+                                        "bytes_per_tick": plan_bytes},
                            "workload": "Gait + FootstepPlanner + FootTrajectoryGenerator + StatePlanner + feet commands, inputs resident in HBM"}
     del pl, pin
     # closed control loop at the reference cadence (Controller.py:246: one MPC solve per k_mpc = 10 ticks) through the C ABI
