@@ -257,18 +257,21 @@ class BatchedInvKin:
 
 class BatchedWbcTick:
     """B robots' ``wbc_controller.compute`` (reference scripts/QP_WBC.py:52-131): Solo12 kinematics / RNEA, InvKin,
-    QPWBC and the feed-forward torque in ONE kernel (a warp per robot; Jc / RNEA never leave the SM).  compute(q, dq, f_cmd, contacts, pgoals, vgoals, agoals) with
+    QPWBC and the feed-forward torque in ONE kernel (groups of 8 / 4 / 2 robots per warp, csrc/wbc_tick_core.cuh; Jc / RNEA never
+    leave the SM; ``group`` fixes the group size, default: chosen from the batch size).  compute(q, dq, f_cmd, contacts, pgoals, vgoals, agoals) with
     q [B,19], dq [B,18], f_cmd [B,12], contacts [B,4], goals [B,12] (3x4 column-major); results in tau_ff, qdes, vdes,
     f_with_delta, ddq_cmd ([B,12] each)."""
 
     kernels_per_tick = 1
 
-    def __init__(self, batch, device=0, debug=False):
+    def __init__(self, batch, device=0, debug=False, group=0):
         self._L = load_library()
         self.B, self.device = int(batch), int(device)
         h = C.c_void_p()
         check(self._L.qrw_wbctick_create(C.byref(h), self.B, self.device))
         self._h = h
+        if group:
+            check(self._L.qrw_wbctick_set_group(self._h, int(group)))
         if debug:  # debug(): also copy the intermediates handed to QPWBC (Jc, RNEA) to HBM every tick
             check(self._L.qrw_wbctick_set_debug(self._h, 1))
         self.tau_ff = self.qdes = self.vdes = self.f_with_delta = self.ddq_cmd = None

@@ -25,12 +25,13 @@ def test_base_inertia_matches_crba(oracle):
     np.testing.assert_allclose(solo12_base_inertia(), np.diag(oracle.solo12_crba(q0))[:6], rtol=1e-12)
 
 
-@pytest.mark.parametrize("level", [True, False])
-def test_wbc_tick_matches_oracle(oracle, level):
+@pytest.mark.parametrize("level,group", [(True, 0), (False, 8), (False, 4), (True, 2)])
+def test_wbc_tick_matches_oracle(oracle, level, group):
+    """B = 301: the last group of 8 / 4 / 2 robots is partly empty; group 0 = the library's own choice."""
     from qrw_b200 import BatchedWbcTick, workloads as wl
 
-    B = 300
-    gpu, cpu = BatchedWbcTick(B, debug=True), oracle.OracleWBC(B)
+    B = 301
+    gpu, cpu = BatchedWbcTick(B, debug=True, group=group), oracle.OracleWBC(B)
     for call in range(3):  # the QP warm start carries over
         args = wl.wbc_tick_inputs(B, seed=40 + call, level_base=level)
         gpu.compute(*args)
@@ -43,6 +44,25 @@ def test_wbc_tick_matches_oracle(oracle, level):
         np.testing.assert_allclose(gpu.vdes, ref["vdes"], rtol=1e-10, atol=1e-10)
         assert_forces_close(gpu.f_with_delta, ref["f_res"], f"f_with_delta call {call}")
         np.testing.assert_allclose(gpu.tau_ff, ref["tau_ff"], rtol=1e-5, atol=1e-4)
+
+
+def test_wbc_tick_does_not_depend_on_the_group_size():
+    """Who shares a robot's warp changes nothing: groups of 8, 4 and 2 give the same bits (two calls, warm start)."""
+    from qrw_b200 import BatchedWbcTick, workloads as wl
+
+    B = 1021
+    res = []
+    for group in (8, 4, 2):
+        gpu = BatchedWbcTick(B, group=group)
+        got = []
+        for call in range(2):
+            gpu.compute(*wl.wbc_tick_inputs(B, seed=60 + call, level_base=False))
+            got.append([a.copy() for a in (gpu.tau_ff, gpu.qdes, gpu.vdes, gpu.f_with_delta, gpu.ddq_cmd)])
+        res.append(got)
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y)
 
 
 def test_wbc_tick_full_size_properties():
