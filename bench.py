@@ -52,9 +52,9 @@ BYTES_PER_SOLVE = 35340  # in 3,556 + out 3,080 + warm-start state
 NCU_DRAM_BYTES_PER_SOLVE = (88.682752e6 + 46.301696e6) / 4096
 DFMA_PEAK_TFLOPS = 34.20  # profiles/r02_fp64_bench.txt (tools/fp64_bench.cu on this pool's B200; cuBLAS DGEMM 8192^3: 35.76)
 # FP64 operations one whole-body tick executes (2 x DFMA + DADD + DMUL thread instructions of one wbc_tick_kernel launch over
-# 65,536 robots, ncu --set full, profiles/r02s_ncu_wbc_tick.txt: 1.727 G DFMA, 0.692 G DADD, 1.589 G DMUL): the kernel is
-# instruction-bound on the FP64 pipe (44 % active), so this is the bound its fraction is quoted against
-WBC_FLOP_PER_TICK = (2 * 1.7271e9 + 0.6917e9 + 1.5890e9) / 65536
+# 65,536 robots, ncu --set full, profiles/r02s_ncu_wbc_tick.txt: 1.727 G DFMA, 0.692 G DADD, 1.356 G DMUL): the kernel is
+# instruction-bound on the FP64 pipe (45 % active), so this is the bound its fraction is quoted against
+WBC_FLOP_PER_TICK = (2 * 1.7271e9 + 0.6917e9 + 1.3557e9) / 65536
 ALL_GAITS = ("trot", "walk", "bounding", "pacing", "static")
 CONFIGS = {
     2: dict(metric="Solo12 MPC QP solves/sec (batched, 16-step)", unit="solves/s", batch=4096, total=None, gaits=("trot",),
@@ -80,8 +80,8 @@ def parse():
     ap.add_argument("--cpu-workers", type=int, default=0, help="worker processes of the CPU arm (0 = one per host core)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU arm (0 = the whole per-GPU workload, capped at 4096)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--work-order", type=int, default=0, choices=[0, 1],
-                    help="0 (default): the persistent MPC grid takes robots in index order; 1: longest-expected-solve first (A/B)")
+    ap.add_argument("--work-order", type=int, default=1, choices=[0, 1],
+                    help="1 (default, the library's default): the persistent MPC grid takes the longest-expected solves first; 0: index order (A/B)")
     ap.add_argument("--wbc-batch", type=int, default=-1,
                     help="robots in the auxiliary whole-body-tick / planner legs (BASELINE config 4); 0 skips them; default 65536 for config 2")
     return ap.parse_args()

@@ -230,30 +230,38 @@ __global__ void __launch_bounds__(nd::NT, 2) mpc_v3_kernel(const MpcConst C, con
 }
 #endif  // QRW_AB_KERNELS
 
-// Work order of the next launch: robots sorted by the ADMM iteration count of their previous solve, longest first
-// (counting sort, one CTA; iteration counts are multiples of check_every = 25 up to max_iter).  The persistent grid
-// pulls robots in this order, so the long solves start early and the grid drains evenly.  Each robot's solve is
-// unchanged -- only when it starts.  OFF by default: a list-scheduling model with a constant time per iteration predicts
-// a 20 % shorter launch for the measured spread of iteration counts (p50 500, p99 1650, max 2300+), but on the B200 a CTA
-// that is alone on its SM at the end of the launch iterates about twice as fast, which already absorbs the tail; measured
-// 40.7 ms (longest first) against 40.0 ms (index order) per 4096-robot step.  Kept as an A/B hook (qrw_mpc_set_work_order).
-__global__ void __launch_bounds__(1024) mpc_order_kernel(const int* __restrict__ info, const int B, int* __restrict__ order) {
+// Work order of a launch: robots sorted by the EXPECTED length of their solve, longest first (counting sort, one CTA;
+// iteration counts are multiples of check_every = 25 up to max_iter).  The persistent grid pulls robots in this order, so the
+// long solves start early and the grid drains evenly; each robot's solve is unchanged -- only when it starts.
+// Why: on config 2 (4096 robots over 296 CTA slots) the iteration counts spread from 250 to 2,500 (mean 580), and in index
+// order a long solve that starts late leaves the other 295 slots idle: a list-scheduling model on the measured counts
+// (tools/tail_model.py, profiles/r02u_tail_model.txt) puts the launch 14 % over the ideal, 0.7 % with the true counts known.
+// The previous tick's count alone does NOT work (measured twice: no gain; the model says why: 15..50 robots per tick jump from
+// ~300 to 1,500+ iterations, and one of them at the END of a longest-first queue costs its whole solve).  Those jumps happen to
+// robots that are commanded to move fast (friction cones active), which the inputs show: the expectation used is
+//   max(previous iteration count, speed_gain * |v_ref,xy|)   with v_ref = xref[6:8, 1]  (speed_gain in iterations per m/s).
+__global__ void __launch_bounds__(1024) mpc_order_kernel(const int* __restrict__ info, const double* __restrict__ xref, const double speed_gain,
+                                                         const int B, int* __restrict__ order) {
   constexpr int NB = 256;
   __shared__ int hist[NB], base[NB];
   for (int i = threadIdx.x; i < NB; i += blockDim.x) hist[i] = 0;
   __syncthreads();
-  auto bucket = [](int it) {
-    int q = NB - 1 - it / 25;  // bucket 0 = the longest
+  auto bucket = [&](int b) {
+    const double* x = xref + (size_t)b * 12 * (NS + 1) + 12;  // column 1: the first reference state
+    const double sp = speed_gain * sqrt(x[6] * x[6] + x[7] * x[7]);
+    const int it = info[4 * b];
+    const int e = sp > (double)it ? (sp < 1e6 ? (int)sp : 1000000) : it;  // a NaN speed compares false: the count is used
+    int q = NB - 1 - e / 25;  // bucket 0 = the longest
     return q < 0 ? 0 : q;
   };
-  for (int b = threadIdx.x; b < B; b += blockDim.x) atomicAdd(&hist[bucket(info[4 * b])], 1);
+  for (int b = threadIdx.x; b < B; b += blockDim.x) atomicAdd(&hist[bucket(b)], 1);
   __syncthreads();
   if (threadIdx.x == 0) {
     int acc = 0;
     for (int i = 0; i < NB; ++i) base[i] = acc, acc += hist[i];
   }
   __syncthreads();
-  for (int b = threadIdx.x; b < B; b += blockDim.x) order[atomicAdd(&base[bucket(info[4 * b])], 1)] = b;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) order[atomicAdd(&base[bucket(b)], 1)] = b;
 }
 
 // gait / S_gait as the doubles the reference getters return (MPC.cpp:770-780)
@@ -471,7 +479,8 @@ struct qrw_mpc {
   double *d_xref = nullptr, *d_fsteps = nullptr, *d_out = nullptr, *d_state = nullptr, *d_rho = nullptr,
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr, *d_order = nullptr;
-  bool use_order = false;  // measured on B200: no gain (40.7 vs 40.0 ms per 4096-robot step), see DESIGN.md 4.1
+  bool use_order = true;       // longest-expected-solve first (mpc_order_kernel); qrw_mpc_set_work_order(h, 0): index order
+  double speed_gain = 2000.0;  // iterations expected per m/s of commanded horizontal speed
   double *h_xref = nullptr, *h_fsteps = nullptr, *h_out = nullptr;  // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;  // recorded behind every solve launch on the CALLER's stream; the host getters wait for it
@@ -684,7 +693,7 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
     if (grid > h->B) grid = h->B;
     const bool ord = h->use_order && h->B > grid;  // the order only matters when CTAs take more than one robot
     if (ord) {
-      mpc_order_kernel<<<1, 1024, 0, s>>>(h->d_info, h->B, h->d_order);
+      mpc_order_kernel<<<1, 1024, 0, s>>>(h->d_info, d_xref, h->speed_gain, h->B, h->d_order);
       ++g_launches;
     }
     mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, h->sms, d_xref, d_fsteps,
@@ -716,7 +725,7 @@ int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xre
   return record_done(h->done, s);
 }
 
-// A/B hook: 0 (default) = robots are taken in index order, 1 = longest-expected-solve first (mpc_order_kernel)
+// 1 (default) = longest-expected-solve first (mpc_order_kernel), 0 = robots are taken in index order
 int qrw_mpc_set_work_order(qrw_mpc_t* h, int longest_first) {
   if (!h) return fail("qrw_mpc_set_work_order: null handle");
   h->use_order = longest_first != 0;

@@ -135,7 +135,7 @@ class BatchedMPC:
         check(self._L.qrw_mpc_set_kernel(self._h, int(variant)))
 
     def set_work_order(self, longest_first):
-        """False (default): the persistent grid takes robots in index order; True: longest-expected-solve first."""
+        """True (default): the persistent grid takes the robots with the longest expected solve first; False: index order."""
         check(self._L.qrw_mpc_set_work_order(self._h, int(bool(longest_first))))
 
     def enable_debug(self):
