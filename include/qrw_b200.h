@@ -169,6 +169,22 @@ int qrw_wbctick_set_debug(qrw_wbctick_t* h, int on);
  * size.  A tuning knob only: results do not depend on it. */
 int qrw_wbctick_set_group(qrw_wbctick_t* h, int group);
 int qrw_wbctick_debug_host(qrw_wbctick_t* h, double* Jc, double* rnea6, double* ddq_res);
+/* ONE whole-body tick that allocates NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernel and same arguments as qrw_wbctick_run_device, but without a handle: the kernel's scratch (QP state, ddq_res,
+ * ddq_cmd, info, work counter, pinv(M)) lives in a file-scope __device__ array of fixed size (csrc/noalloc_abi.cuh, 3.0 MB,
+ * held by every GPU that loads the library until the process exits); the call issues one cudaMemsetAsync of 4 bytes and one
+ * kernel launch on `stream` and calls no cudaMalloc / cudaFree / allocating routine.  All pointers are DEVICE pointers of the
+ * caller: q [B][19], dq [B][18], f_cmd [B][12], contacts [B][4], goals [B][12] in; tau_ff, qdes, vdes, f_res [B][12] out.
+ * LIMITS: batch <= QRW_WBCTICK_NOALLOC_MAX_ROBOTS, anything larger is rejected with an error; the QP is always cold-started
+ * (a call equals the FIRST qrw_wbctick_run_device of a fresh handle -- a warm start needs state between calls, i.e. a
+ * handle); every call on a device shares the one array, which keeps the last call's contents (the call clears what must start
+ * at zero): calls that OVERLAP on the GPU race, serialise them; the first call on a device does a one-time set-up
+ * (cudaGetSymbolAddress, constants, one device synchronisation): make it outside graph capture. */
+#define QRW_WBCTICK_NOALLOC_MAX_ROBOTS 4096
+int qrw_wbctick_noalloc_device(int batch, int device, const double* q, const double* dq, const double* f_cmd, const double* contacts,
+                               const double* pgoals, const double* vgoals, const double* agoals, double* tau_ff, double* qdes,
+                               double* vdes, double* f_res, void* stream);
 /* diag(crba(q = 0)[:6, :6]): (m, m, m, Ixx, Iyy, Izz) of the whole robot about the base frame */
 int qrw_solo12_base_inertia(double* Y6);
 /* what solo12InvKin.py:47-59 reads from Pinocchio: q12, dq12 [B][12] -> posf, vf, wf, af [B][4*3], Jf [B][12*12] */

@@ -1204,3 +1204,4 @@ int qrw_solo12_feet_host(int batch, const double* q12, const double* dq12, doubl
 #include "tick_abi.cuh"
 #include <time.h>
 #include "transport_abi.cuh"
+#include "noalloc_abi.cuh"

@@ -106,6 +106,7 @@ _SIGNATURES = {
     "qrw_wbctick_debug_host": (C.c_int, [_vp] * 4),
     "qrw_wbctick_set_debug": (C.c_int, [_vp, C.c_int]),
     "qrw_wbctick_set_group": (C.c_int, [_vp, C.c_int]),
+    "qrw_wbctick_noalloc_device": (C.c_int, [C.c_int, C.c_int] + [_vp] * 11 + [_vp]),
     "qrw_wbctick_set_desired_host": (C.c_int, [_vp, _vp, _vp]),
     "qrw_wbctick_run_ctrl_device": (C.c_int, [_vp, C.c_double, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "qrw_solo12_base_inertia": (C.c_int, [_vp]),
