@@ -26,7 +26,7 @@ SMALL="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --wbc-batch 65536"
 timeout 300 $SMALL > $OUT/small.json 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:mpc_v2_kernel -s 5 -c 1 -f -o $OUT/prof_mpc $SMALL > $OUT/ncu_full.log 2>&1
 echo "ncu mpc rc=$?" | tee -a $OUT/rc.txt
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"wbc_" -s 9 -c 3 -f -o $OUT/prof_wbc $SMALL > $OUT/ncu_wbc.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"wbc_tick_kernel" -s 4 -c 2 -f -o $OUT/prof_wbc $SMALL > $OUT/ncu_wbc.log 2>&1
 echo "ncu wbc rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:planner_tick_kernel -s 10 -c 2 -f -o $OUT/prof_planner $SMALL > $OUT/ncu_planner.log 2>&1
 echo "ncu planner rc=$?" | tee -a $OUT/rc.txt
