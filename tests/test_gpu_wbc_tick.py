@@ -80,3 +80,22 @@ def test_wbc_tick_full_size_properties():
     assert (fz > -1e-3).all() and (fz < 25 + 1e-3).all()
     assert (np.abs(f[..., 0]) <= 0.9 * fz + 1e-3).all() and (np.abs(f[..., 1]) <= 0.9 * fz + 1e-3).all()
     assert np.isfinite(gpu.tau_ff).all()
+
+
+def test_wbc_tick_full_size_sampled_against_oracle(oracle):
+    """BASELINE config 4 at its full size (65,536 robots, groups of eight per warp, every CTA slot of the GPU busy): 256 robots
+    sampled across the batch are recomputed by the oracle from the same inputs (cold start: robots are independent)."""
+    from qrw_b200 import BatchedWbcTick, workloads as wl
+
+    B = 65536
+    args = wl.wbc_tick_inputs(B, seed=9, level_base=False)
+    gpu = BatchedWbcTick(B)
+    gpu.compute(*args)
+    pick = np.unique(np.concatenate([np.arange(0, B, 257), [B - 1, B - 2, B - 9]]))
+    sub = [np.ascontiguousarray(a[pick]) for a in args]
+    ref = oracle.wbc_tick(oracle.OracleWBC(len(pick)), *sub, nthreads=8)
+    assert_forces_close(gpu.f_with_delta[pick], ref["f_res"], "f_with_delta, sampled robots")
+    np.testing.assert_allclose(gpu.tau_ff[pick], ref["tau_ff"], rtol=1e-5, atol=1e-4)
+    np.testing.assert_allclose(gpu.qdes[pick], ref["qdes"], rtol=1e-10, atol=1e-10)
+    np.testing.assert_allclose(gpu.vdes[pick], ref["vdes"], rtol=1e-10, atol=1e-10)
+    np.testing.assert_allclose(gpu.ddq_cmd[pick], ref["ddq_cmd"], rtol=1e-9, atol=1e-8)
