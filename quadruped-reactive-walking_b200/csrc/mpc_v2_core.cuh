@@ -1152,17 +1152,26 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         }
         var_acc(R.dX * vx, (cscale * C.w[j] * R.dX * R.dX) * R.xX, R.dX);
       }
+      // The termination test needs the six UNSCALED norms (odd q); the scaled ones (even q) feed the rho estimate only, on every
+      // (adapt_every / check_every)-th check: their reductions are skipped otherwise.  Across the warps, lane q reduces column
+      // q (same order as before: warp 0, 1, .. 7) and broadcasts it, instead of every thread reading all 96 partial maxima.
+      const bool adapt_now = (iter % C.adapt_every == 0);
 #pragma unroll
       for (int q = 0; q < 12; ++q) {
-        m[q] = cta::warp_max(m[q]);
-        if (l == 0) S.red[16 + 12 * w + q] = m[q];
+        if (adapt_now || (q & 1)) {
+          m[q] = cta::warp_max_x(m[q]);
+          if (l == 0) S.red[16 + 12 * w + q] = m[q];
+        }
       }
       cta::bar();
+      {
+        const int lq = l < 12 ? l : 11;
+        double v = S.red[16 + lq];
 #pragma unroll
-      for (int q = 0; q < 12; ++q) {
-        double v = S.red[16 + q];
-        for (int ww = 1; ww < NT / 32; ++ww) v = dmax(v, S.red[16 + 12 * ww + q]);
-        m[q] = v;
+        for (int ww = 1; ww < NT / 32; ++ww) v = dmax(v, S.red[16 + 12 * ww + lq]);
+#pragma unroll
+        for (int q = 0; q < 12; ++q)
+          if (adapt_now || (q & 1)) m[q] = cta::bcast(v, q);
       }
       const double pri_s = m[0], pri_u = m[1], nz_s = m[2], nz_u = m[3], nax_s = m[4], nax_u = m[5], dua_s = m[6],
                    dua_u = cinv * m[7], naty_s = m[8], naty_u = m[9], npx_s = m[10], npx_u = m[11];
@@ -1181,7 +1190,7 @@ QRW_HD void mpc_v2_solve(const MpcConst& C, double* slab, const double* xref, co
         const double t2 = 10.0 * C.eps_abs + 10.0 * C.eps_rel * (cinv * dmax(naty_u, npx_u));
         status = (pri_u < t1 && dua_u < t2) ? ST_SOLVED_INACCURATE : ST_MAX_ITER;
       }
-      if (iter % C.adapt_every == 0) {
+      if (adapt_now) {
         const double pr = pri_s / (dmax(nz_s, nax_s) + 1e-10);
         const double dr = dua_s / (dmax(naty_s, npx_s) + 1e-10);
         double est = Rh.rho * sqrt(pr / (dr + 1e-10));

@@ -117,6 +117,13 @@ __device__ __forceinline__ bool any(bool p) { return __any_sync(0xffffffffu, p) 
 // value held by lane `src` (0..15) of the caller's 16-lane group
 __device__ __forceinline__ double shfl16(double v, int src) { return __shfl_sync(0xffffffffu, v, src, 16); }
 __device__ __forceinline__ double shfl_xor(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+// warp_max / shfl on the explicitly unpacked pair (the MPC residual check: 72 shuffles per check)
+__device__ __forceinline__ double warp_max_x(double v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v = fmax(v, shfl_bfly64(v, m));
+  return v;
+}
+__device__ __forceinline__ double bcast(double v, int src) { return shfl_idx64(v, src, 0x1f); }
 // the same two on the explicitly unpacked pair (whole-body tick)
 __device__ __forceinline__ double hshfl(double v, int src) { return shfl_idx64(v, src, 0x101f); }
 __device__ __forceinline__ double hxor(double v, int m) { return shfl_bfly64(v, m); }
@@ -263,6 +270,8 @@ int fetch_add(int* p, int v);
 bool any(bool p);
 double shfl16(double v, int src);
 double shfl_xor(double v, int m);
+inline double warp_max_x(double v) { return warp_max(v); }
+inline double bcast(double v, int src) { return shfl(v, src); }
 inline double hshfl(double v, int src) { return shfl16(v, src); }
 inline double hxor(double v, int m) { return shfl_xor(v, m); }
 inline void sched_fence() {}
