@@ -452,7 +452,9 @@ def run_b200(args):
         "config": {"workload": cfg["workload"], "bench_config": args.config, "batch_per_gpu": B, "total_robots": world * B, "n_steps": 16,
                    "N_gait": 20, "history": "tick 0 cold (untimed) then update ticks, closed loop",
                    "l2": "256 MiB flush write between timed steps", "sharding": f"instances, {world} rank(s), all_gather of f0 only, pipelined with the next step's solve"},
-        "e2e": {"value": e2e_value, "unit": cfg["unit"], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "e2e": {"value": e2e_value, "unit": cfg["unit"], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "transfer": "MPC inputs and results cross PCIe inside the timed region, zero-copy: the kernel reads each robot's inputs "
+                            "from the pinned host buffers and writes its result to the pinned result buffer, under the solves"},
         "gpu_launches": int(launches),
         "roofline": roof, "roofline_hbm": roof_hbm, "cpu_baseline": cpu, "clocks": clocks,
         "latency_ms": {"p50": float(np.percentile(step_ms, 50)), "p99": float(np.percentile(step_ms, 99)), "max": float(step_ms.max())},

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
                                                            const double* __restrict__ fsteps, double* st_d,
                                                            int* st_i, double* out, int* info, double* rho,
                                                            double* dbg, int* counter, const int* __restrict__ k_arr,
-                                                           const int* __restrict__ order) {
+                                                           const int* __restrict__ order, double* __restrict__ out_host) {
   extern __shared__ __align__(16) double slab[];
   int* next = reinterpret_cast<int*>(slab + v2::V_INT) + 127;
   const int recw = (blockIdx.x / sms) & 3;
@@ -143,6 +143,12 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
                      st_d + (size_t)b * MPC_STATE_DOUBLES, st_i + (size_t)b * MPC_STATE_INTS, f,
                      out + (size_t)b * 24 * NS, info + 4 * b, rho + b, dbg ? dbg + (size_t)b * 1281 : nullptr, recw, tmem);
     __syncthreads();
+    if (out_host) {  // host entry point: the robot's result also goes straight to the pinned (UVA-mapped) host buffer, under the
+                     // solves of the other robots, instead of one device-to-host copy of everything behind the launch
+      const double* o = out + (size_t)b * 24 * NS;
+      double* oh = out_host + (size_t)b * 24 * NS;
+      for (int i = threadIdx.x; i < 24 * NS; i += v2::NT) oh[i] = o[i];
+    }
   }
   cta::tmem_free(tmem);
 }
@@ -482,6 +488,9 @@ struct qrw_mpc {
   bool use_order = true;       // longest-expected-solve first (mpc_order_kernel); qrw_mpc_set_work_order(h, 0): index order
   double speed_gain = 2000.0;  // iterations expected per m/s of commanded horizontal speed
   double *h_xref = nullptr, *h_fsteps = nullptr, *h_out = nullptr;  // pinned
+  double* h_out_dev = nullptr;   // device-side address of h_out (UVA mapping), nullptr if the mapping is not available
+  double* mirror_next = nullptr;  // set by qrw_mpc_run_host around its launch: the kernel mirrors every result into h_out
+  bool host_fresh = false;        // h_out holds the results of the latest solve (qrw_mpc_result_host(h, h_out) has nothing to copy)
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;  // recorded behind every solve launch on the CALLER's stream; the host getters wait for it
 };
@@ -618,6 +627,11 @@ int qrw_mpc_create(qrw_mpc_t** out, int batch, double dt, int n_steps, double T_
   CUH(cudaMallocHost(&h->h_xref, B * 12 * (NS + 1) * sizeof(double)), qrw_mpc_destroy(h));
   CUH(cudaMallocHost(&h->h_fsteps, B * 12 * N_gait * sizeof(double)), qrw_mpc_destroy(h));
   CUH(cudaMallocHost(&h->h_out, B * 24 * NS * sizeof(double)), qrw_mpc_destroy(h));
+  {  // under unified addressing pinned host memory is mapped into the device's address space: kernels can write it
+    void* dp = nullptr;
+    if (cudaHostGetDevicePointer(&dp, h->h_out, 0) == cudaSuccess) h->h_out_dev = static_cast<double*>(dp);
+    else cudaGetLastError();
+  }
   CUH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), qrw_mpc_destroy(h));
   CUH(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming), qrw_mpc_destroy(h));
   CUH(cudaFuncSetAttribute(mpc_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::V2_SLAB_BYTES), qrw_mpc_destroy(h));
@@ -658,6 +672,7 @@ int qrw_mpc_destroy(qrw_mpc_t* h) {
 int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const double* d_fsteps, void* stream) {
   if (!h || !d_xref || !d_fsteps) return fail("qrw_mpc_run_device: null argument");
   CU(cudaSetDevice(h->device));
+  h->host_fresh = false;
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
 #ifdef QRW_AB_KERNELS
@@ -699,7 +714,7 @@ int qrw_mpc_run_device(qrw_mpc_t* h, int num_iter, const double* d_xref, const d
     mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, num_iter == 0 ? 1 : 0, h->sms, d_xref, d_fsteps,
                                                           h->d_state, h->d_state_i, h->d_out, h->d_info, h->d_rho,
                                                           h->dbg_on ? h->d_dbg : nullptr, h->d_counter, nullptr,
-                                                          ord ? h->d_order : nullptr);
+                                                          ord ? h->d_order : nullptr, h->mirror_next);
   }
   ++g_launches;
   CU(cudaGetLastError());
@@ -713,13 +728,14 @@ int qrw_mpc_run_indexed_device(qrw_mpc_t* h, const int* d_k, const double* d_xre
   if (!h || !d_k || !d_xref || !d_fsteps) return fail("qrw_mpc_run_indexed_device: null argument");
   if (h->variant != 2) return fail("qrw_mpc_run_indexed_device: only the default kernel (variant 2) takes a per-robot index");
   CU(cudaSetDevice(h->device));
+  h->host_fresh = false;
   cudaStream_t s = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_counter, 0, sizeof(int), s));
   int grid = 2 * h->sms;
   if (grid > h->B) grid = h->B;
   mpc_v2_kernel<<<grid, v2::NT, v2::V2_SLAB_BYTES, s>>>(h->C, h->B, 0, h->sms, d_xref, d_fsteps, h->d_state, h->d_state_i, h->d_out,
                                                         h->d_info, h->d_rho, h->dbg_on ? h->d_dbg : nullptr, h->d_counter, d_k,
-                                                        nullptr);
+                                                        nullptr, nullptr);
   ++g_launches;
   CU(cudaGetLastError());
   return record_done(h->done, s);
@@ -732,20 +748,46 @@ int qrw_mpc_set_work_order(qrw_mpc_t* h, int longest_first) {
   return 0;
 }
 
+// device-side address of a pinned (page-locked, UVA-mapped) host pointer; nullptr for pageable memory
+static const double* mapped_host_ptr(const double* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return (a.type == cudaMemoryTypeHost && a.devicePointer) ? static_cast<const double*>(a.devicePointer) : nullptr;
+}
+
+// Host entry point.  Pageable inputs are staged with two copies.  PINNED inputs (cudaMallocHost / cudaHostRegister / torch
+// pin_memory: e.g. the handle's own buffers, qrw_mpc_pinned) are not copied at all: the kernel reads each robot's xref / fsteps
+// straight from host memory when it starts on that robot (3.5 KB over PCIe against a ~6 ms solve) and mirrors the robot's result
+// into the handle's pinned result buffer when it is done, so both transfers run under the solves of the other robots instead of
+// in front of and behind the launch.
 int qrw_mpc_run_host(qrw_mpc_t* h, int num_iter, const double* xref, const double* fsteps) {
   if (!h || !xref || !fsteps) return fail("qrw_mpc_run_host: null argument");
   CU(cudaSetDevice(h->device));
   const size_t B = (size_t)h->B;
-  CU(cudaMemcpyAsync(h->d_xref, xref, B * 12 * (NS + 1) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  CU(cudaMemcpyAsync(h->d_fsteps, fsteps, B * 12 * h->N_gait * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  if (qrw_mpc_run_device(h, num_iter, h->d_xref, h->d_fsteps, h->stream)) return 1;
+  const double* mx = h->variant == 2 ? mapped_host_ptr(xref) : nullptr;
+  const double* mf = mx ? mapped_host_ptr(fsteps) : nullptr;
+  const bool zero_copy = mx && mf;
+  if (!zero_copy) {
+    CU(cudaMemcpyAsync(h->d_xref, xref, B * 12 * (NS + 1) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_fsteps, fsteps, B * 12 * h->N_gait * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  }
+  h->mirror_next = zero_copy ? h->h_out_dev : nullptr;
+  const bool mirrored = h->mirror_next != nullptr;
+  const int rc = qrw_mpc_run_device(h, num_iter, zero_copy ? mx : h->d_xref, zero_copy ? mf : h->d_fsteps, h->stream);
+  h->mirror_next = nullptr;
+  if (rc) return 1;
   CU(cudaStreamSynchronize(h->stream));
+  h->host_fresh = mirrored;
   return 0;
 }
 
 int qrw_mpc_result_host(qrw_mpc_t* h, double* out) {
   if (!h || !out) return fail("qrw_mpc_result_host: null argument");
   CU(cudaSetDevice(h->device));
+  if (h->host_fresh && out == h->h_out) return 0;  // the kernel has written it there already (qrw_mpc_run_host, pinned inputs)
   CU(cudaStreamWaitEvent(h->stream, h->done, 0));  // the last solve may have been launched on another stream
   CU(cudaMemcpyAsync(out, h->d_out, (size_t)h->B * 24 * NS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));

@@ -67,3 +67,44 @@ def test_non_finite_input_of_one_robot_does_not_touch_its_neighbours(oracle):
     assert not np.isfinite(rg[3]).all()
     assert gpu.info()["status"][3] == cpu.info()["status"][3]
     assert gpu.info()["iters"][3] == cpu.info()["iters"][3]
+
+
+def test_pinned_host_buffers_take_the_zero_copy_path_with_identical_results():
+    """qrw_mpc_run_host with PINNED inputs: the kernel reads xref / fsteps straight from host memory and mirrors every result into
+    the handle's pinned result buffer (no staging copies).  Same bits as the pageable path: results (read through the pinned
+    buffer and through an ordinary array), iteration counts, gait, three ticks of a mixed-gait closed loop; and a device-side run
+    afterwards must not be answered from the stale host mirror."""
+    import torch
+
+    from qrw_b200 import BatchedMPC, workloads as wl
+
+    B = 600  # more robots than CTA slots: CTAs take several robots each
+    w = wl.MpcWorkload(B, 23, gaits=("trot", "walk", "bounding", "pacing", "static"), ticks=4)
+    a, b = BatchedMPC(B), BatchedMPC(B)
+    px, pf, pr = b.pinned()
+    x0 = None
+    for t in range(3):
+        xr, fs = w.inputs(t, x0)
+        a.run(t, xr, fs)  # pageable numpy arrays: staged
+        px[:], pf[:] = xr, fs
+        pr[:] = np.nan
+        b.run(t, px, pf)  # the handle's pinned buffers: zero copy
+        ra = a.get_latest_result()
+        rb_pinned = b.get_latest_result(out=pr)
+        assert rb_pinned is pr and np.array_equal(ra, pr), f"tick {t}: pinned result buffer"
+        assert np.array_equal(ra, b.get_latest_result()), f"tick {t}: ordinary result array"
+        assert np.array_equal(a.info()["iters"], b.info()["iters"]) and np.array_equal(a.get_gait(), b.get_gait())
+        x0 = ra[:, :12].copy()
+    # a torch pinned tensor is the same kind of memory
+    xr, fs = w.inputs(3, x0)
+    tx, tf = torch.from_numpy(xr).pin_memory(), torch.from_numpy(fs).pin_memory()
+    a.run(3, xr, fs)
+    b.run(3, tx.numpy(), tf.numpy())
+    assert np.array_equal(a.get_latest_result(), b.get_latest_result(out=pr))
+    # device-side run: the mirror is stale now, the getter must copy
+    dx, df = torch.from_numpy(w.inputs(4 if False else 3, x0)[0]).cuda(), torch.from_numpy(fs).cuda()
+    pr[:] = np.nan
+    b.run(4, dx, df)
+    a.run(4, xr, fs)
+    torch.cuda.synchronize()
+    assert np.array_equal(a.get_latest_result(), b.get_latest_result(out=pr))
