@@ -378,6 +378,12 @@ def run_b200(args):
     mpc.state_load(snap)
     torch.cuda.synchronize()
 
+    f_pin = tick_out = None
+    if full:  # pinned host buffers for the tick's force input and its five outputs
+        f_pin = pinned_like(np.zeros((B, 12))).numpy()
+        tick_out_t = [pinned_like(np.zeros((B, 12))) for _ in range(5)]
+        tick_out = [t_.numpy() for t_ in tick_out_t]
+
     def step_host(t):
         hx, hf = host_in[0 if lazy_host else t]
         if lazy_host:
@@ -388,8 +394,9 @@ def run_b200(args):
         mpc.get_latest_result(out=pin_r)
         if full:
             a = [x.numpy() for x in targs_h]
-            a[2] = np.ascontiguousarray(pin_r[:, 12:24])  # x_f_mpc[12:24, 0] (Controller.py:258) on the host, as the reference does
-            tick.compute(*a)
+            np.copyto(f_pin, pin_r[:, 12:24])  # x_f_mpc[12:24, 0] (Controller.py:258) on the host, as the reference does
+            a[2] = f_pin
+            tick.compute(*a, out=tick_out)
         return time.perf_counter() - t_
 
     for t in range(W):
@@ -589,8 +596,16 @@ def aux_legs(args, L, dev, local, rank, world, B, K, W, Bw, mpc, snap, dev_in, r
     barrier()
     period_ms = np.array([a.elapsed_time(b) for a, b in pev])
     ct = max_over_ranks(float(period_ms.sum()))
-    hstk = [stack(p_) for p_ in range(2 + K, 2 + 2 * K)]
-    outs = [np.empty((10, B, 12)) for _ in range(3)]
+    def pin(a):  # pinned host memory (the e2e contract): a torch pinned tensor behind a numpy view of the same dtype
+        t = torch.empty(a.shape, dtype=torch.from_numpy(a[:0].copy()).dtype).pin_memory()
+        v = t.numpy()
+        v[...] = a
+        pin.keep.append(t)
+        return v
+
+    pin.keep = []
+    hstk = [[pin(a) for a in stack(p_)] for p_ in range(2 + K, 2 + 2 * K)]
+    outs = [pin(np.empty((10, B, 12))) for _ in range(3)]
     barrier()
     t0 = time.perf_counter()
     for h_ in hstk:

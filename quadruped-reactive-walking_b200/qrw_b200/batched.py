@@ -283,7 +283,9 @@ class BatchedWbcTick:
 
     __del__ = close
 
-    def compute(self, q, dq, f_cmd, contacts, pgoals, vgoals, agoals, fetch=True):
+    def compute(self, q, dq, f_cmd, contacts, pgoals, vgoals, agoals, fetch=True, out=None):
+        """out (optional, host path): five [B, 12] float64 arrays that receive tau_ff, qdes, vdes, f_with_delta, ddq_cmd (e.g.
+        pinned buffers, so that the device-to-host copies are not staged through pageable memory)."""
         B = self.B
         sizes = [19, 18, 12, 4, 12, 12, 12]
         args = [q, dq, f_cmd, contacts, pgoals, vgoals, agoals]
@@ -293,7 +295,9 @@ class BatchedWbcTick:
         a = [_host(x, B * s) for x, s in zip(args, sizes)]
         check(self._L.qrw_wbctick_run_host(self._h, *[x.ctypes.data for x in a]))
         if fetch:
-            outs = [np.empty((B, 12)) for _ in range(5)]
+            outs = [np.empty((B, 12)) for _ in range(5)] if out is None else list(out)
+            if len(outs) != 5 or any(o.dtype != np.float64 or not o.flags.c_contiguous or o.size != B * 12 for o in outs):
+                raise ValueError("out must be five contiguous float64 arrays of B*12 elements")
             check(self._L.qrw_wbctick_result_host(self._h, *[o.ctypes.data for o in outs]))
             self.tau_ff, self.qdes, self.vdes, self.f_with_delta, self.ddq_cmd = outs
         return 0
