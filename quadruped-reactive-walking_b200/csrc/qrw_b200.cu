@@ -486,7 +486,10 @@ struct qrw_mpc {
          *d_dbg = nullptr, *d_gait = nullptr, *d_sgait = nullptr;
   int *d_state_i = nullptr, *d_info = nullptr, *d_counter = nullptr, *d_order = nullptr;
   bool use_order = true;       // longest-expected-solve first (mpc_order_kernel); qrw_mpc_set_work_order(h, 0): index order
-  double speed_gain = 2000.0;  // iterations expected per m/s of commanded horizontal speed
+#ifndef QRW_SPEED_GAIN
+#define QRW_SPEED_GAIN 2000.0
+#endif
+  double speed_gain = QRW_SPEED_GAIN;  // iterations expected per m/s of commanded horizontal speed
   double *h_xref = nullptr, *h_fsteps = nullptr, *h_out = nullptr;  // pinned
   double* h_out_dev = nullptr;   // device-side address of h_out (UVA mapping), nullptr if the mapping is not available
   double* mirror_next = nullptr;  // set by qrw_mpc_run_host around its launch: the kernel mirrors every result into h_out

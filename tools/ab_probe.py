@@ -10,7 +10,7 @@ from qrw_b200 import BatchedMPC, _lib, workloads as wl
 variants = [int(a) for a in sys.argv[1:]] or [2, 4]
 AB = os.environ.get("QRW_LIB", _lib._AB_SO)  # QRW_LIB: any other build of the library (then variant 2 only)
 B, T = 4096, 8
-w = wl.MpcWorkload(B, 1, gaits=("trot",), ticks=T + 2)
+w = wl.MpcWorkload(B, int(os.environ.get("AB_SEED", "1")), gaits=("trot",), ticks=T + 2)
 dev = torch.device("cuda", 0)
 ref = None
 for v in variants:
