@@ -48,8 +48,8 @@ import numpy as np  # noqa: E402
 UNIT = "solves/s"
 BYTES_PER_SOLVE = 35340  # in 3,556 + out 3,080 + warm-start state r/w 28,704
 # dram__bytes_read.sum + dram__bytes_write.sum of one mpc_v2_kernel launch over 4096 robots, ncu --set full
-# (profiles/r02p_ncu_mpc_v2.txt: 88.68 MB + 46.30 MB), per robot: no re-reads beyond the algorithmic bytes
-NCU_DRAM_BYTES_PER_SOLVE = (88.682752e6 + 46.301696e6) / 4096
+# (profiles/r02x_ncu_mpc_v2.txt: 88.57 MB + 47.44 MB), per robot: no re-reads beyond the algorithmic bytes
+NCU_DRAM_BYTES_PER_SOLVE = (88.568320e6 + 47.444736e6) / 4096
 DFMA_PEAK_TFLOPS = 34.20  # profiles/r02_fp64_bench.txt (tools/fp64_bench.cu on this pool's B200; cuBLAS DGEMM 8192^3: 35.76)
 # FP64 operations one whole-body tick executes (2 x DFMA + DADD + DMUL thread instructions of one wbc_tick_kernel launch over
 # 65,536 robots, ncu --set full, profiles/r02s_ncu_wbc_tick.txt: 1.727 G DFMA, 0.692 G DADD, 1.356 G DMUL): the kernel is
@@ -431,7 +431,7 @@ def run_b200(args):
                            "cuBLAS DGEMM 35.76 TFLOP/s); MEASURED_PEAKS.json holds no FP64 figure",
             "flop_model": "workloads.FLOP_PER_ADMM_ITER (44,408: the block-tridiagonal ADMM iteration of DESIGN.md) x measured mean "
                           "ADMM iterations + FLOP_PER_SETUP",
-            "traffic_source": "dram bytes of one launch, ncu --set full (profiles/r02p_ncu_mpc_v2.txt), scaled by batch"}
+            "traffic_source": "dram bytes of one launch, ncu --set full (profiles/r02x_ncu_mpc_v2.txt), scaled by batch"}
     if hasattr(L, "qrw_fp64_peak"):
         import ctypes as C
 
