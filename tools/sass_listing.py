@@ -8,7 +8,7 @@ import sys
 import tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SO = os.path.join(ROOT, "quadruped-reactive-walking_b200", "libqrw_b200.so")
+SO = os.environ.get("QRW_LIB", os.path.join(ROOT, "quadruped-reactive-walking_b200", "libqrw_b200.so"))
 SRC = os.path.join(ROOT, "quadruped-reactive-walking_b200", "csrc", "mpc_v2_core.cuh")
 out_path = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r02_sass_mpc_v2_loop_and_chain.txt")
 
