@@ -63,6 +63,7 @@ def lib():
         L.orc_pinv6.argtypes = [_dp, _dp]
         L.orc_invkin_run.argtypes = [C.c_int] + [_dp] * 12
         L.orc_osqp_dense.argtypes = [C.c_int, C.c_int] + [_dp] * 5 + [C.c_double, C.c_int, _dp, _dp, _ip]
+        L.orc_osqp_dense_ex.argtypes = ([C.c_int, C.c_int] + [_dp] * 5 + [C.c_double, C.c_double, C.c_int, C.c_int, _dp, _dp, _ip, _dp])
         L.orc_solo12_feet.argtypes = [C.c_int] + [_dp] * 7
         L.orc_solo12_rnea.argtypes = [C.c_int] + [_dp] * 4
         L.orc_solo12_jc.argtypes = [C.c_int] + [_dp] * 3
@@ -227,6 +228,20 @@ def osqp_dense(P, A, q, l, u, eps=1e-8, max_iter=20000):
     it = np.zeros(1, np.int32)
     st = lib().orc_osqp_dense(n, m, _d(P), _d(A), _d(q), _d(l), _d(u), float(eps), int(max_iter), _d(x), _d(y), _i(it))
     return x, y, int(it[0]), st
+
+
+def osqp_dense_ex(P, A, q, l, u, eps=1e-3, alpha=1.6, max_iter=4000, adaptive_rho_interval=0):
+    """Restated OSQP with its DEFAULT settings except those given; returns (x, y, iters, status, info) with the last iterate
+    (also when max_iter stops the run) and info = dict(pri_res, dua_res, rho, rho_updates, rho_estimate): what OSQP prints."""
+    P = np.asfortranarray(P, dtype=np.float64)
+    A = np.asfortranarray(A, dtype=np.float64)
+    m, n = A.shape
+    q, l, u = _c(q), _c(l), _c(u)
+    x, y, info = np.empty(n), np.empty(m), np.empty(5)
+    it = np.zeros(1, np.int32)
+    st = lib().orc_osqp_dense_ex(n, m, _d(P), _d(A), _d(q), _d(l), _d(u), float(eps), float(alpha), int(max_iter),
+                                 int(adaptive_rho_interval), _d(x), _d(y), _i(it), _d(info))
+    return x, y, int(it[0]), st, dict(pri_res=info[0], dua_res=info[1], rho=info[2], rho_updates=int(info[3]), rho_estimate=info[4])
 
 
 # ---------------------------------------------------------------------------------------------

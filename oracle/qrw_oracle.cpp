@@ -832,4 +832,40 @@ int orc_osqp_dense(int n, int m, const double* Pd, const double* Ad, const doubl
   return o.status;
 }
 
+// The same with alpha and the adaptive-rho interval chosen by the caller (0 = OSQP's rule without PROFILING: 4 x
+// check_termination), OSQP's default tolerances unless eps says otherwise, and what OSQP prints returned: the last iterate
+// (also when max_iter stops the run -- max_iter = 1 gives the figures of OSQP's "iter 1" line), info5 = {pri_res, dua_res, rho,
+// number of rho updates, rho estimate at the end}.  tests/test_oracle_pins.py compares them with the output printed in OSQP's
+// own documentation.
+int orc_osqp_dense_ex(int n, int m, const double* Pd, const double* Ad, const double* q, const double* l, const double* u,
+                      double eps, double alpha, int max_iter, int adaptive_rho_interval, double* x_out, double* y_out,
+                      int* iters, double* info5) {
+  std::vector<int> r, c;
+  std::vector<double> v;
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i <= j; ++i)
+      if (Pd[i + n * j] != 0.0 || i == j) r.push_back(i), c.push_back(j), v.push_back(Pd[i + n * j]);
+  Csc P = triplet_to_csc(n, n, r, c, v);
+  r.clear(), c.clear(), v.clear();
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i < m; ++i)
+      if (Ad[i + m * j] != 0.0) r.push_back(i), c.push_back(j), v.push_back(Ad[i + m * j]);
+  Csc A = triplet_to_csc(m, n, r, c, v);
+  Settings s;
+  s.eps_abs = eps;
+  s.eps_rel = eps;
+  s.alpha = alpha;
+  s.max_iter = max_iter;
+  s.adaptive_rho_interval = adaptive_rho_interval;
+  Osqp o;
+  o.setup(P, A, q, l, u, s);
+  o.solve();
+  for (int j = 0; j < n; ++j) x_out[j] = o.st.scaling ? o.D[j] * o.x[j] : o.x[j];
+  for (int i = 0; i < m; ++i) y_out[i] = o.st.scaling ? o.E[i] * o.y[i] * o.cinv : o.y[i];
+  *iters = o.iter;
+  info5[0] = o.pri_res, info5[1] = o.dua_res, info5[2] = o.st.rho, info5[3] = (double)o.rho_updates;
+  info5[4] = o.compute_rho_estimate();
+  return o.status;
+}
+
 }  // extern "C"

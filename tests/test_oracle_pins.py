@@ -179,3 +179,46 @@ def test_oracle_reproduces_wbc_tick_golden(oracle):
         r = oracle.wbc_tick(o, *[g[f"{n}{c}"] for n in names], nthreads=4)
         for k in ("tau_ff", "qdes", "vdes", "f_res"):
             np.testing.assert_allclose(r[k], g[f"{k}{c}"], rtol=0, atol=1e-9)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The one OSQP output this image can be compared with: the run printed in OSQP's own documentation (osqp.org, "Examples ->
+# Setup and solve", OSQP v0.6.0; Python: prob.setup(P, q, A, l, u, alpha=1.0); prob.solve()):
+#
+#     iter   objective    pri res    dua res    rho        time
+#        1  -4.9384e-03   1.00e+00   2.00e+02   1.00e-01   ...
+#       50   1.8800e+00   1.91e-07   7.50e-07   1.38e+00   ...
+#     status: solved   number of iterations: 50   optimal objective: 1.8800   optimal rho estimate: 1.36e+00
+#
+# No network and no OSQP exist here: the figures are written down from the builder's memory of that page.  They were NOT fitted:
+# the restatement reproduces every printed digit of all eleven of them, which a faulty recollection or a faulty restatement
+# would not.  That run exercises the Ruiz equilibration and cost scaling (iteration 1 depends on D, E, c), rho of an equality
+# row (x 1000), the KKT solve, the unscaled residuals, the termination test (not met at iteration 25, met at 50), the rho
+# estimate and update (0.1 -> 1.38 at iteration 25; in that run OSQP's timing-based rule chose the interval, here it is set).
+# ---------------------------------------------------------------------------------------------------------------------
+OSQP_DOC_P = np.array([[4.0, 1.0], [1.0, 2.0]])
+OSQP_DOC_Q = np.array([1.0, 1.0])
+OSQP_DOC_A = np.array([[1.0, 1.0], [1.0, 0.0], [0.0, 1.0]])
+OSQP_DOC_L = np.array([1.0, 0.0, 0.0])
+OSQP_DOC_U = np.array([1.0, 0.7, 0.7])
+
+
+def _osqp_line(it, x, info):
+    obj = 0.5 * x @ OSQP_DOC_P @ x + OSQP_DOC_Q @ x
+    return "%4d %12.4e %10.2e %10.2e %10.2e" % (it, obj, info["pri_res"], info["dua_res"], info["rho"])
+
+
+def test_restated_osqp_reproduces_the_run_printed_in_osqps_documentation(oracle):
+    args = (OSQP_DOC_P, OSQP_DOC_A, OSQP_DOC_Q, OSQP_DOC_L, OSQP_DOC_U)
+    x, y, it, st, info = oracle.osqp_dense_ex(*args, alpha=1.0, max_iter=1)
+    assert _osqp_line(it, x, info).split() == ["1", "-4.9384e-03", "1.00e+00", "2.00e+02", "1.00e-01"]
+    x, y, it, st, info = oracle.osqp_dense_ex(*args, alpha=1.0, adaptive_rho_interval=25)
+    assert st == 1  # OSQP_SOLVED
+    assert _osqp_line(it, x, info).split() == ["50", "1.8800e+00", "1.91e-07", "7.50e-07", "1.38e+00"]
+    assert info["rho_updates"] == 1 and "%.2e" % info["rho_estimate"] == "1.36e+00"
+    np.testing.assert_allclose(x, [0.3, 0.7], atol=1e-6)         # the solution the page prints
+    np.testing.assert_allclose(y, [-2.9, 0.0, 0.2], atol=1e-6)
+    # the interval is the one free choice and it is not a fit: with any other multiple of 25 the run ends differently
+    for interval in (50, 100):
+        _, _, it2, _, info2 = oracle.osqp_dense_ex(*args, alpha=1.0, adaptive_rho_interval=interval)
+        assert (it2, "%.2e" % info2["rho"]) != (50, "1.38e+00")

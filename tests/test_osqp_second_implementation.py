@@ -107,3 +107,17 @@ def test_second_implementation_follows_the_same_iterates(oracle, seed):
     assert it1 == it2, f"ADMM iterations: restatement {it1}, second implementation {it2}"
     np.testing.assert_allclose(x1, x2, rtol=1e-7, atol=1e-9)
     np.testing.assert_allclose(y1, y2, rtol=1e-6, atol=1e-8)
+
+
+def test_second_implementation_reproduces_the_run_printed_in_osqps_documentation():
+    """The same published run as tests/test_oracle_pins.py::test_restated_osqp_reproduces_the_run_printed_in_osqps_documentation
+    (P = [[4, 1], [1, 2]], q = [1, 1], A = [[1, 1], [1, 0], [0, 1]], l = [1, 0, 0], u = [1, 0.7, 0.7], alpha = 1.0), through
+    the numpy implementation: objective after iteration 1, and 50 iterations to the printed solution."""
+    P, q = np.array([[4.0, 1.0], [1.0, 2.0]]), np.array([1.0, 1.0])
+    A, l, u = np.array([[1.0, 1.0], [1.0, 0.0], [0.0, 1.0]]), np.array([1.0, 0.0, 0.0]), np.array([1.0, 0.7, 0.7])
+    x, _, _, _ = osqp_numpy(P, A, q, l, u, 1e-3, max_iter=1, alpha=1.0, check=1000, interval=1000)
+    assert "%.4e" % (0.5 * x @ P @ x + q @ x) == "-4.9384e-03"
+    x, y, it, _ = osqp_numpy(P, A, q, l, u, 1e-3, alpha=1.0, interval=25)
+    assert it == 50 and "%.4e" % (0.5 * x @ P @ x + q @ x) == "1.8800e+00"
+    np.testing.assert_allclose(x, [0.3, 0.7], atol=1e-6)
+    np.testing.assert_allclose(y, [-2.9, 0.0, 0.2], atol=1e-6)
