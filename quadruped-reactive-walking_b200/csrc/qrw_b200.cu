@@ -119,7 +119,11 @@ __global__ void __launch_bounds__(v2::NT, 2) mpc_v2_kernel(const MpcConst C, con
                                                            const int* __restrict__ order, double* __restrict__ out_host) {
   extern __shared__ __align__(16) double slab[];
   int* next = reinterpret_cast<int*>(slab + v2::V_INT) + 127;
-  const int recw = (blockIdx.x / sms) & 3;
+  // first of the three chain warps (elimination, helper, back-substitution): warps 0..2 in the first wave of CTAs, 2..4 in the
+  // second, so that the two CTAs that share an SM keep their elimination warps on different SM sub-partitions and the second
+  // CTA's elimination shares one with the first CTA's back-substitution.  Measured (tools/ab_probe.py, 4096 robots): offset 2
+  // (or 6) 162.1 k solves/s, offset 1 (round 1's choice) 160.4 k, offsets 0 / 4 160.5 k, offset 3 159.5 k.
+  const int recw = ((blockIdx.x / sms) * 2) & 7;
   // 256 of the SM's 512 tensor-memory columns for the whole life of this (persistent) CTA: the matrix rows of the solve
   const unsigned tmem = cta::tmem_alloc(reinterpret_cast<unsigned*>(slab + v2::V_INT) + v2::V2_TMEM_SLOT);
   for (;;) {
